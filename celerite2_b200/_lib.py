@@ -1,0 +1,78 @@
+"""ctypes binding of libcelerite2_b200.so (the C ABI declared in include/celerite2_b200.h).
+
+There is no CPU fallback: if the shared library is missing the import fails, and every compute call fails
+when no CUDA device is visible.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcelerite2_b200.so")
+
+_vp = ctypes.c_void_p
+_i64 = ctypes.c_int64
+_i32 = ctypes.c_int32
+_sz = ctypes.c_size_t
+
+OP_IDS = {
+    "factor": 0, "factor_rev": 1, "solve_lower": 2, "solve_upper": 3, "matmul_lower": 4, "matmul_upper": 5,
+    "solve_lower_rev": 6, "solve_upper_rev": 7, "matmul_lower_rev": 8, "matmul_upper_rev": 9,
+    "general_matmul": 10, "assemble_rev": 11,
+}
+SHARED_T, SHARED_C, SHARED_Y = 1, 2, 4
+
+# name -> argument types (return type is int unless listed in _RESTYPE); mirrors include/celerite2_b200.h
+_SIGS = {
+    "c2b_get_celerite_matrices": [_i32, _i64, _i32, _i32, _i64] + [_vp] * 12 + [_i32, _vp],
+    "c2b_get_celerite_matrices_rev": [_i32, _i64, _i32, _i32, _i64] + [_vp] * 19 + [_i32, _vp, _sz, _vp],
+    "c2b_factor": [_i64, _i32, _i64] + [_vp] * 9 + [_i32, _vp, _sz, _vp],
+    "c2b_factor_rev": [_i64, _i32, _i64] + [_vp] * 15 + [_i32, _vp, _sz, _vp],
+    "c2b_general_matmul_lower": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
+    "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
+    "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
+}
+for _op in ("solve_lower", "solve_upper", "matmul_lower", "matmul_upper"):
+    _SIGS["c2b_" + _op] = [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp]
+    _SIGS["c2b_" + _op + "_rev"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp]
+
+EXPORTS = sorted(list(_SIGS) + ["c2b_version", "c2b_last_error", "c2b_device_count", "c2b_scratch_bytes", "c2b_set_chunks_per_series"])
+
+
+class C2BError(RuntimeError):
+    pass
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "celerite2_b200: %s is missing. Build it with `python -m celerite2_b200.build` (needs nvcc); "
+            "there is no CPU fallback." % LIB_PATH
+        )
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, args in _SIGS.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = ctypes.c_int
+    lib.c2b_version.restype = ctypes.c_char_p
+    lib.c2b_version.argtypes = []
+    lib.c2b_last_error.restype = ctypes.c_char_p
+    lib.c2b_last_error.argtypes = []
+    lib.c2b_device_count.restype = _i32
+    lib.c2b_device_count.argtypes = []
+    lib.c2b_scratch_bytes.restype = _sz
+    lib.c2b_scratch_bytes.argtypes = [_i32, _i64, _i64, _i32, _i32, _i64]
+    lib.c2b_set_chunks_per_series.restype = None
+    lib.c2b_set_chunks_per_series.argtypes = [_i64]
+    return lib
+
+
+lib = _load()
+
+
+def check(rc):
+    if rc != 0:
+        raise C2BError("celerite2_b200 error %d: %s" % (rc, lib.c2b_last_error().decode()))
+
+
+def version():
+    return lib.c2b_version().decode()

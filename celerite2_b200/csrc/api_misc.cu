@@ -1,0 +1,282 @@
+// C ABI: library plumbing, assembly (+ adjoint), log-det / chi^2 reductions, general_matmul.
+#include <stdarg.h>
+#include <stdlib.h>
+
+#include "host_common.cuh"
+#include "misc.cuh"
+
+namespace c2b {
+
+static thread_local char g_err[512] = "";
+static int64_t g_chunk_override    = -1;  // -1: not yet read from the environment
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? C2B_ERR_NO_DEVICE : C2B_ERR_CUDA;
+}
+
+int64_t get_chunk_override() {
+  if (g_chunk_override < 0) {
+    const char *s    = getenv("C2B_CHUNKS");
+    g_chunk_override = s ? atoll(s) : 0;
+    if (g_chunk_override < 0) g_chunk_override = 0;
+  }
+  return g_chunk_override;
+}
+
+// Chunks along N exist only to expose parallelism: batch * cols * C independent units should fill the GPU
+// (148 SMs x a few warps).  Short chunks would be dominated by the summary pass, so L >= 64.
+Plan make_plan(int64_t N, int64_t batch, int64_t cols) {
+  Plan pl;
+  pl.N     = N;
+  pl.batch = batch;
+  int64_t C;
+  const int64_t ov = get_chunk_override();
+  if (ov > 0) {
+    C = ov;
+  } else {
+    const int64_t target = 8192;
+    const int64_t have   = batch * (cols > 0 ? cols : 1);
+    C                    = have >= target ? 1 : (target + have - 1) / have;
+    const int64_t maxC   = N / 64;
+    if (C > maxC) C = maxC;
+  }
+  if (C > N) C = N;
+  if (C < 1) C = 1;
+  if (C > 32768) C = 32768;
+  pl.L = (N + C - 1) / C;
+  pl.C = (N + pl.L - 1) / pl.L;
+  return pl;
+}
+
+int Scratch::init(void *user, size_t user_bytes, size_t need, cudaStream_t s) {
+  stream = s;
+  if (need == 0) return C2B_OK;
+  if (user) {
+    if (user_bytes < need) {
+      set_error("scratch buffer too small: need %zu bytes, got %zu", need, user_bytes);
+      return C2B_ERR_SCRATCH_TOO_SMALL;
+    }
+    ptr   = user;
+    bytes = user_bytes;
+    return C2B_OK;
+  }
+  C2B_CUDA(cudaMallocAsync(&ptr, need, s));
+  bytes = need;
+  owned = true;
+  return C2B_OK;
+}
+Scratch::~Scratch() {
+  if (owned && ptr) cudaFreeAsync(ptr, stream);
+}
+
+size_t scratch_general_matmul(int64_t M, int J, int K) {
+  Arena ar = sizing_arena();
+  Plan pl  = make_plan(M, 1, K);
+  ScanBuffers sb;
+  if (pl.C > 1) take_scan(ar, 1, pl.C, J + J * K, J * K, &sb);
+  ar.take<double>((size_t)M * J * K);
+  return ar.used;
+}
+static int asm_rev_ctas(int64_t N) {
+  int64_t c = (N + kAsmRevThreads * 4 - 1) / (kAsmRevThreads * 4);
+  if (c > 592) c = 592;
+  if (c < 1) c = 1;
+  return (int)c;
+}
+size_t scratch_assemble_rev(int64_t N, int Jr, int Jc, int64_t batch) {
+  return align256((size_t)batch * asm_rev_ctas(N) * (Jr + 3 * Jc) * sizeof(double));
+}
+static int red_ctas(int64_t N) {
+  int64_t c = (N + kRedThreads * 8 - 1) / (kRedThreads * 8);
+  if (c > 592) c = 592;
+  if (c < 1) c = 1;
+  return (int)c;
+}
+size_t scratch_norm_logdet(int64_t N, int64_t batch) { return align256((size_t)batch * red_ctas(N) * 2 * sizeof(double)); }
+
+template <bool UPPER>
+static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double *t1, const double *t2, const double *c, const double *U,
+                                const double *V, const double *Y, double *Z, double *F, void *scratch, size_t scratch_bytes,
+                                void *stream_) {
+  int rc = check_common(N, J, 1);
+  if (rc) return rc;
+  C2B_REQUIRE(M >= 1 && K >= 1, "M and K must be >= 1");
+  C2B_REQUIRE(t1 && t2 && c && U && V && Y && Z, "null data pointer");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Scratch sc;
+  rc = sc.init(scratch, scratch_bytes, scratch_general_matmul(M, J, K), stream);
+  if (rc) return rc;
+  Arena ar(sc.ptr, sc.bytes);
+  Plan pl = make_plan(M, 1, K);
+  ScanBuffers sb;
+  if (pl.C > 1) take_scan(ar, 1, pl.C, J + J * K, J * K, &sb);
+  GmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.N = N; g.M = M; g.C = pl.C; g.L = pl.L; g.J = J; g.K = K;
+  g.t1 = t1; g.t2 = t2; g.c = c; g.U = U; g.V = V; g.Y = Y; g.Z = Z;
+  g.H    = ar.take<double>((size_t)M * J * K);
+  g.Fout = F;
+  unsigned grid, block;
+  launch_shape(pl.C * K, &grid, &block);
+  if (pl.C > 1) {
+    g.leaves      = sb.nodes;
+    g.node_stride = sb.node_stride;
+    gm_scan_kernel<UPPER, true><<<grid, block, 0, stream>>>(g);
+    C2B_CHECK_LAUNCH();
+    rc = run_scan<DiagV<0>>(J, K, 1, pl.C, sb.nodes, sb.states, nullptr, stream);
+    if (rc) return rc;
+    g.carry = sb.states;
+  }
+  gm_scan_kernel<UPPER, false><<<grid, block, 0, stream>>>(g);
+  C2B_CHECK_LAUNCH();
+  gm_gather_kernel<UPPER><<<(unsigned)((N * K + 127) / 128), 128, 0, stream>>>(g);
+  C2B_CHECK_LAUNCH();
+  if (F) {
+    gm_workspace_kernel<UPPER><<<(unsigned)((M * (int64_t)J * K + 127) / 128), 128, 0, stream>>>(g);
+    C2B_CHECK_LAUNCH();
+  }
+  return C2B_OK;
+}
+
+}  // namespace c2b
+
+extern "C" {
+
+const char *c2b_version(void) { return "celerite2_b200 0.1.0 (sm_100a)"; }
+const char *c2b_last_error(void) { return c2b::g_err; }
+
+int32_t c2b_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+void c2b_set_chunks_per_series(int64_t chunks) { c2b::g_chunk_override = chunks > 0 ? chunks : 0; }
+
+size_t c2b_scratch_bytes(int32_t op, int64_t N, int64_t M, int32_t J, int32_t K, int64_t batch) {
+  using namespace c2b;
+  if (N < 1 || J < 1 || batch < 1) return 0;
+  if (K < 1) K = 1;
+  switch (op) {
+    case C2B_OP_FACTOR: return scratch_factor(N, J, batch);
+    case C2B_OP_FACTOR_REV: return scratch_factor_rev(N, J, batch);
+    case C2B_OP_SOLVE_LOWER:
+    case C2B_OP_SOLVE_UPPER: return scratch_sweep(true, N, J, K, batch);
+    case C2B_OP_MATMUL_LOWER:
+    case C2B_OP_MATMUL_UPPER: return scratch_sweep(false, N, J, K, batch);
+    case C2B_OP_SOLVE_LOWER_REV:
+    case C2B_OP_SOLVE_UPPER_REV: return scratch_sweep_rev(true, N, J, K, batch);
+    case C2B_OP_MATMUL_LOWER_REV:
+    case C2B_OP_MATMUL_UPPER_REV: return scratch_sweep_rev(false, N, J, K, batch);
+    case C2B_OP_GENERAL_MATMUL: return scratch_general_matmul(M > 0 ? M : N, J, K);
+    case C2B_OP_ASSEMBLE_REV: return scratch_assemble_rev(N, J, J, batch);  // upper bound: Jr, Jc <= J
+    default: return 0;
+  }
+}
+
+int c2b_get_celerite_matrices(int32_t layout, int64_t N, int32_t Jr, int32_t Jc, int64_t batch, const double *ar, const double *cr,
+                              const double *ac, const double *bc, const double *cc, const double *dc, const double *x,
+                              const double *diag, double *c_out, double *a_out, double *U_out, double *V_out, int32_t flags,
+                              void *stream_) {
+  using namespace c2b;
+  C2B_REQUIRE(Jr >= 0 && Jc >= 0, "negative term count");
+  int rc = check_common(N, Jr + 2 * Jc, batch);
+  if (rc) return rc;
+  C2B_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (blocked) or 1 (interleaved)");
+  C2B_REQUIRE(x && diag && a_out && U_out && V_out, "null data pointer");
+  C2B_REQUIRE((Jr == 0 || (ar && cr)) && (Jc == 0 || (ac && bc && cc && dc)), "null coefficient pointer");
+  AsmArgs g;
+  memset(&g, 0, sizeof(g));
+  g.N = N; g.batch = batch; g.Jr = Jr; g.Jc = Jc; g.layout = layout;
+  g.ar = ar; g.cr = cr; g.ac = ac; g.bc = bc; g.cc = cc; g.dc = dc; g.x = x; g.diag = diag;
+  g.c_out = c_out; g.a_out = a_out; g.U_out = U_out; g.V_out = V_out;
+  g.x_bs    = (flags & C2B_SHARED_T) ? 0 : N;
+  g.co_r_bs = (flags & C2B_SHARED_C) ? 0 : Jr;
+  g.co_c_bs = (flags & C2B_SHARED_C) ? 0 : Jc;
+  const int64_t total = batch * N;
+  assemble_kernel<<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream_>>>(g);
+  C2B_CHECK_LAUNCH();
+  return C2B_OK;
+}
+
+int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t Jc, int64_t batch, const double *ar, const double *cr,
+                                  const double *ac, const double *bc, const double *cc, const double *dc, const double *x,
+                                  const double *b_c, const double *b_a, const double *b_U, const double *b_V, double *b_ar,
+                                  double *b_cr, double *b_ac, double *b_bc, double *b_cc, double *b_dc, double *b_x, double *b_diag,
+                                  int32_t flags, void *scratch, size_t scratch_bytes, void *stream_) {
+  using namespace c2b;
+  (void)cr;
+  (void)cc;
+  C2B_REQUIRE(Jr >= 0 && Jc >= 0, "negative term count");
+  int rc = check_common(N, Jr + 2 * Jc, batch);
+  if (rc) return rc;
+  C2B_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (blocked) or 1 (interleaved)");
+  C2B_REQUIRE(x && b_a && b_U && b_V, "null data pointer");
+  C2B_REQUIRE((Jr == 0 || (ar && b_ar && b_cr)) && (Jc == 0 || (ac && bc && dc && b_ac && b_bc && b_cc && b_dc)),
+              "null coefficient pointer");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Scratch sc;
+  rc = sc.init(scratch, scratch_bytes, scratch_assemble_rev(N, Jr, Jc, batch), stream);
+  if (rc) return rc;
+  AsmRevArgs g;
+  memset(&g, 0, sizeof(g));
+  g.N = N; g.batch = batch; g.Jr = Jr; g.Jc = Jc; g.layout = layout;
+  g.ar = ar; g.ac = ac; g.bc = bc; g.dc = dc; g.x = x;
+  g.b_c = b_c; g.b_a = b_a; g.b_U = b_U; g.b_V = b_V;
+  g.b_ar = b_ar; g.b_cr = b_cr; g.b_ac = b_ac; g.b_bc = b_bc; g.b_cc = b_cc; g.b_dc = b_dc; g.b_x = b_x; g.b_diag = b_diag;
+  g.x_bs    = (flags & C2B_SHARED_T) ? 0 : N;
+  g.co_r_bs = (flags & C2B_SHARED_C) ? 0 : Jr;
+  g.co_c_bs = (flags & C2B_SHARED_C) ? 0 : Jc;
+  g.part    = (double *)sc.ptr;
+  g.ctas_per_series = asm_rev_ctas(N);
+  const int nred    = Jr + 3 * Jc;
+  dim3 grid((unsigned)g.ctas_per_series, (unsigned)batch);
+  assemble_rev_kernel<<<grid, kAsmRevThreads, (size_t)nred * kAsmRevThreads * sizeof(double), stream>>>(g);
+  C2B_CHECK_LAUNCH();
+  assemble_rev_final_kernel<<<(unsigned)batch, 64, 0, stream>>>(g);
+  C2B_CHECK_LAUNCH();
+  return C2B_OK;
+}
+
+int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd, void *scratch,
+                    size_t scratch_bytes, void *stream_) {
+  using namespace c2b;
+  int rc = check_common(N, 1, batch);
+  if (rc) return rc;
+  C2B_REQUIRE(d && z && out, "null data pointer");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Scratch sc;
+  rc = sc.init(scratch, scratch_bytes, scratch_norm_logdet(N, batch), stream);
+  if (rc) return rc;
+  const int ctas = red_ctas(N);
+  dim3 grid((unsigned)ctas, (unsigned)batch);
+  norm_logdet_kernel<<<grid, kRedThreads, 0, stream>>>(N, d, z, bz, bd, (double *)sc.ptr, ctas);
+  C2B_CHECK_LAUNCH();
+  norm_logdet_final_kernel<<<(unsigned)batch, 32, 0, stream>>>((const double *)sc.ptr, ctas, out);
+  C2B_CHECK_LAUNCH();
+  return C2B_OK;
+}
+
+int c2b_general_matmul_lower(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
+                             const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
+                             size_t scratch_bytes, void *stream) {
+  return c2b::general_matmul_entry<false>(N, M, J, K, t1, t2, c, U, V, Y, Z, F, scratch, scratch_bytes, stream);
+}
+int c2b_general_matmul_upper(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
+                             const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
+                             size_t scratch_bytes, void *stream) {
+  return c2b::general_matmul_entry<true>(N, M, J, K, t1, t2, c, U, V, Y, Z, F, scratch, scratch_bytes, stream);
+}
+
+}  // extern "C"

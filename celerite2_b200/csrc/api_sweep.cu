@@ -1,0 +1,166 @@
+// C ABI: solve_lower / solve_upper / matmul_lower / matmul_upper and their reverse-mode counterparts.
+#include "host_common.cuh"
+
+namespace c2b {
+
+static int sizes_sweep(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb) {
+  *pl = make_plan(N, batch, K);
+  if (pl->C > 1) {
+    const int es = solve ? J * J + J * K : J + J * K;
+    take_scan(ar, batch, pl->C, es, J * K, sb);
+  }
+  return C2B_OK;
+}
+
+size_t scratch_sweep(bool solve, int64_t N, int J, int K, int64_t batch) {
+  Plan pl;
+  Arena ar = sizing_arena();
+  ScanBuffers sb;
+  sizes_sweep(solve, N, J, K, batch, &pl, ar, &sb);
+  return ar.used;
+}
+
+static int sizes_sweep_rev(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb, double **bc_part,
+                           double **bt_edge) {
+  *pl = make_plan(N, batch, K);
+  if (pl->C > 1) {
+    const int es = solve ? J * J + J * K : J + J * K;
+    take_scan(ar, batch, pl->C, es, J * K, sb);
+  }
+  *bc_part = ar.take<double>((size_t)batch * pl->C * J);
+  *bt_edge = ar.take<double>((size_t)batch * pl->C);
+  return C2B_OK;
+}
+
+size_t scratch_sweep_rev(bool solve, int64_t N, int J, int K, int64_t batch) {
+  Plan pl;
+  Arena ar = sizing_arena();
+  ScanBuffers sb;
+  double *a, *b;
+  sizes_sweep_rev(solve, N, J, K, batch, &pl, ar, &sb, &a, &b);
+  return ar.used;
+}
+
+
+template <bool SOLVE, bool LOWER>
+static int sweep_entry(int64_t N, int J, int K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                       const double *Y, double *Z, double *F, int flags, void *scratch, size_t scratch_bytes, void *stream_) {
+  int rc = check_common(N, J, batch);
+  if (rc) return rc;
+  C2B_REQUIRE(K >= 1, "K (number of right-hand sides) must be >= 1");
+  C2B_REQUIRE(t && c && U && W && Y && Z, "null data pointer");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Plan pl;
+  ScanBuffers sb;
+  {
+    Arena sz = sizing_arena();
+    sizes_sweep(SOLVE, N, J, K, batch, &pl, sz, &sb);
+    Scratch sc;
+    rc = sc.init(scratch, scratch_bytes, sz.used, stream);
+    if (rc) return rc;
+    Arena ar(sc.ptr, sc.bytes);
+    sizes_sweep(SOLVE, N, J, K, batch, &pl, ar, &sb);
+    SweepArgs a;
+    memset(&a, 0, sizeof(a));
+    a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.K = K;
+    a.t = t; a.c = c; a.Y = Y; a.Z = Z; a.F = F;
+    a.A = LOWER ? U : W;
+    a.B = LOWER ? W : U;
+    a.t_bs = (flags & C2B_SHARED_T) ? 0 : N;
+    a.c_bs = (flags & C2B_SHARED_C) ? 0 : J;
+    a.y_bs = (flags & C2B_SHARED_Y) ? 0 : N * (int64_t)K;
+    if (SOLVE && (flags & C2B_SHARED_Y) && batch > 1) C2B_REQUIRE(Z != Y, "in-place solve needs a per-series Y");
+#define CALL(JT) rc = launch_sweep<JT, SOLVE, LOWER>(a, sb, stream)
+    C2B_DISPATCH_J_SWEEP(J, CALL)
+#undef CALL
+    return rc;
+  }
+}
+
+
+template <bool SOLVE, bool LOWER>
+static int sweep_rev_entry(int64_t N, int J, int K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                           const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc, double *bU,
+                           double *bW, double *bY, int flags, void *scratch, size_t scratch_bytes, void *stream_) {
+  int rc = check_common(N, J, batch);
+  if (rc) return rc;
+  C2B_REQUIRE(K >= 1, "K (number of right-hand sides) must be >= 1");
+  C2B_REQUIRE(t && c && U && W && Y && Z && F && bZ && bt && bc && bU && bW && bY, "null data pointer");
+  cudaStream_t stream = (cudaStream_t)stream_;
+  Plan pl;
+  ScanBuffers sb;
+  double *bc_part, *bt_edge;
+  Arena sz = sizing_arena();
+  sizes_sweep_rev(SOLVE, N, J, K, batch, &pl, sz, &sb, &bc_part, &bt_edge);
+  Scratch sc;
+  rc = sc.init(scratch, scratch_bytes, sz.used, stream);
+  if (rc) return rc;
+  Arena ar(sc.ptr, sc.bytes);
+  sizes_sweep_rev(SOLVE, N, J, K, batch, &pl, ar, &sb, &bc_part, &bt_edge);
+  SweepRevArgs a;
+  memset(&a, 0, sizeof(a));
+  a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.K = K;
+  a.t = t; a.c = c; a.Y = Y; a.Z = Z; a.F = F; a.bZ = bZ;
+  a.A = LOWER ? U : W;
+  a.B = LOWER ? W : U;
+  a.bt = bt; a.bY = bY;
+  a.bA = LOWER ? bU : bW;
+  a.bB = LOWER ? bW : bU;
+  a.t_bs = (flags & C2B_SHARED_T) ? 0 : N;
+  a.c_bs = (flags & C2B_SHARED_C) ? 0 : J;
+  a.y_bs = (flags & C2B_SHARED_Y) ? 0 : N * (int64_t)K;
+  a.bc_part = bc_part;
+  a.bt_edge = bt_edge;
+#define CALL(JT) rc = launch_sweep_rev<JT, SOLVE, LOWER>(a, sb, bc, stream)
+  C2B_DISPATCH_J_SWEEP(J, CALL)
+#undef CALL
+  return rc;
+}
+
+}  // namespace c2b
+
+extern "C" {
+
+int c2b_solve_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                    const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, F, flags, scratch, scratch_bytes, stream);
+}
+int c2b_solve_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                    const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_entry<true, false>(N, J, K, batch, t, c, U, W, Y, Z, F, flags, scratch, scratch_bytes, stream);
+}
+int c2b_matmul_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *V,
+                     const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_entry<false, true>(N, J, K, batch, t, c, U, V, Y, Z, F, flags, scratch, scratch_bytes, stream);
+}
+int c2b_matmul_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *V,
+                     const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_entry<false, false>(N, J, K, batch, t, c, U, V, Y, Z, F, flags, scratch, scratch_bytes, stream);
+}
+
+int c2b_solve_lower_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                        const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
+                        double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_rev_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, F, bZ, bt, bc, bU, bW, bY, flags, scratch, scratch_bytes,
+                                          stream);
+}
+int c2b_solve_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                        const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
+                        double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_rev_entry<true, false>(N, J, K, batch, t, c, U, W, Y, Z, F, bZ, bt, bc, bU, bW, bY, flags, scratch, scratch_bytes,
+                                           stream);
+}
+int c2b_matmul_lower_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                         const double *V, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
+                         double *bU, double *bV, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_rev_entry<false, true>(N, J, K, batch, t, c, U, V, Y, Z, F, bZ, bt, bc, bU, bV, bY, flags, scratch, scratch_bytes,
+                                           stream);
+}
+int c2b_matmul_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                         const double *V, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
+                         double *bU, double *bV, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  return c2b::sweep_rev_entry<false, false>(N, J, K, batch, t, c, U, V, Y, Z, F, bZ, bt, bc, bU, bV, bY, flags, scratch, scratch_bytes,
+                                            stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,128 @@
+// Shared device/host helpers for the celerite2_b200 kernels (sm_100a, FP64 throughout).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <math.h>
+
+#include "../../include/celerite2_b200.h"
+
+#define C2B_DEV __device__ __forceinline__
+
+// Compile-time width JT in 1..8 or 16 gives register arrays and fully unrolled loops; JT == 0 is the
+// run-time-width fallback (J <= C2B_MAX_J, arrays live in local memory).
+template <int JT>
+struct Width {
+  static constexpr int MAXJ = JT > 0 ? JT : C2B_MAX_J;
+  static constexpr int UNR  = (JT > 0 && JT <= 8) ? JT : 1;  // unroll factor for loops over J
+};
+#define C2B_PRAGMA(x) _Pragma(#x)
+#define C2B_UNROLL_J C2B_PRAGMA(unroll Width<JT>::UNR)
+
+namespace c2b {
+
+// ---- error reporting (host) ---------------------------------------------------------------------------------
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what);
+#define C2B_CUDA(call)                                                                                                                    \
+  do {                                                                                                                                    \
+    cudaError_t _e = (call);                                                                                                              \
+    if (_e != cudaSuccess) return c2b::cuda_fail(_e, #call);                                                                              \
+  } while (0)
+#define C2B_CHECK_LAUNCH() C2B_CUDA(cudaGetLastError())
+#define C2B_REQUIRE(cond, msg)                                                                                                            \
+  do {                                                                                                                                    \
+    if (!(cond)) {                                                                                                                        \
+      c2b::set_error("%s: %s", __func__, msg);                                                                                            \
+      return C2B_ERR_INVALID_ARGUMENT;                                                                                                    \
+    }                                                                                                                                     \
+  } while (0)
+
+// ---- chunk plan ---------------------------------------------------------------------------------------------
+// A series of N points is cut into C chunks of L points (the last one shorter).  Chunks are the unit of
+// parallelism along N; carries between chunks come from an associative scan over per-chunk summaries.
+struct Plan {
+  int64_t N, batch;
+  int64_t C;  // chunks per series
+  int64_t L;  // points per chunk
+};
+Plan make_plan(int64_t N, int64_t batch, int64_t cols);
+int64_t get_chunk_override();
+
+static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// Bump allocator over the caller's scratch buffer.
+struct Arena {
+  char *base;
+  size_t size, used;
+  bool overflow;
+  Arena(void *p, size_t n) : base((char *)p), size(n), used(0), overflow(false) {}
+  template <typename T>
+  T *take(size_t count) {
+    size_t bytes = align256(count * sizeof(T));
+    if (used + bytes > size) {
+      overflow = true;
+      return nullptr;
+    }
+    T *r = (T *)(base + used);
+    used += bytes;
+    return r;
+  }
+};
+
+// RAII scratch: uses the caller's buffer or allocates one on the stream.
+struct Scratch {
+  void *ptr    = nullptr;
+  size_t bytes = 0;
+  bool owned   = false;
+  cudaStream_t stream;
+  int init(void *user, size_t user_bytes, size_t need, cudaStream_t s);
+  ~Scratch();
+};
+
+}  // namespace c2b
+
+// ---- device helpers -----------------------------------------------------------------------------------------
+// p[j] = exp(c[j] * dt), computing each distinct value of c once: complex terms contribute pairs of equal
+// c (c++/include/celerite2/terms.hpp:125, python/celerite2/terms.py:172-173).  dup[j] is a bitmask of earlier
+// indices i < j with c[i] == c[j] (0 => compute).
+template <int JT>
+C2B_DEV void dup_masks(int J, const double *c, unsigned *dup) {
+  C2B_UNROLL_J
+  for (int j = 0; j < J; ++j) {
+    unsigned m = 0;
+    C2B_UNROLL_J
+    for (int i = 0; i < J; ++i)
+      if (i < j && c[i] == c[j] && m == 0) m = 1u << i;
+    dup[j] = m;
+  }
+}
+
+template <int JT>
+C2B_DEV void compute_p(int J, const double *c, const unsigned *dup, double dt, double *p) {
+  C2B_UNROLL_J
+  for (int j = 0; j < J; ++j) {
+    if (dup[j] == 0) {
+      p[j] = exp(c[j] * dt);
+    } else {
+      double v = 0.0;
+      C2B_UNROLL_J
+      for (int i = 0; i < J; ++i)
+        if (i < j && ((dup[j] >> i) & 1u)) v = p[i];
+      p[j] = v;
+    }
+  }
+}
+
+// First failing row of factor(): keep the smallest positive index (0 = success).
+C2B_DEV void record_failure(int64_t *status, int64_t n) {
+  if (!status) return;
+  unsigned long long *s   = (unsigned long long *)status;
+  unsigned long long old = atomicCAS(s, 0ull, (unsigned long long)n);
+  while (old != 0ull && (unsigned long long)n < old) {
+    unsigned long long prev = atomicCAS(s, old, (unsigned long long)n);
+    if (prev == old) break;
+    old = prev;
+  }
+}

@@ -1,0 +1,69 @@
+// Launchers of the sweep kernels for ONE compile-time width (C2B_JT); see args.cuh.
+#include "host_common.cuh"
+#include "sweep.cuh"
+
+#ifndef C2B_JT
+#error "compile with -DC2B_JT=<width> (0 = run-time width)"
+#endif
+
+namespace c2b {
+
+template <int JT, bool SOLVE, bool LOWER>
+int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  unsigned grid, block;
+  if (a.C > 1) {
+    a.leaves      = sb.nodes;
+    a.node_stride = sb.node_stride;
+    const int ncol = SOLVE ? a.J + a.K : a.K;
+    launch_shape(a.batch * a.C * ncol, &grid, &block);
+    sweep_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
+    C2B_CHECK_LAUNCH();
+    int rc;
+    if (SOLVE)
+      rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+    else
+      rc = run_scan<DiagV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+    if (rc) return rc;
+    a.carry = sb.states;
+  }
+  launch_shape(a.batch * a.C * a.K, &grid, &block);
+  sweep_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
+  C2B_CHECK_LAUNCH();
+  return C2B_OK;
+}
+
+template <int JT, bool SOLVE, bool LOWER>
+int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
+  unsigned grid, block;
+  if (a.C > 1) {
+    a.leaves      = sb.nodes;
+    a.node_stride = sb.node_stride;
+    const int ncol = SOLVE ? a.J + a.K : a.K;
+    launch_shape(a.batch * a.C * ncol, &grid, &block);
+    sweep_rev_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
+    C2B_CHECK_LAUNCH();
+    int rc;
+    if (SOLVE)
+      rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+    else
+      rc = run_scan<DiagV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+    if (rc) return rc;
+    a.carry = sb.states;
+  }
+  launch_shape(a.batch * a.C, &grid, &block);
+  sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
+  C2B_CHECK_LAUNCH();
+  rev_finalize_kernel<<<(unsigned)a.batch, 256, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc);
+  C2B_CHECK_LAUNCH();
+  return C2B_OK;
+}
+
+#define INST(S, L)                                                                                                                        \
+  template int launch_sweep<C2B_JT, S, L>(SweepArgs &, const ScanBuffers &, cudaStream_t);                                                \
+  template int launch_sweep_rev<C2B_JT, S, L>(SweepRevArgs &, const ScanBuffers &, double *, cudaStream_t);
+INST(true, true)
+INST(true, false)
+INST(false, true)
+INST(false, false)
+
+}  // namespace c2b

@@ -1,0 +1,187 @@
+// Generic exclusive scan of chunk summaries ("elements") into per-chunk carry-in states.
+//
+// The chunks of a series, taken in PROCESSING order (ascending n for forward sweeps, descending for backward
+// ones), are the leaves of a binary tree stored level by level:
+//   up-sweep    node[l][i] = combine(node[l-1][2i], node[l-1][2i+1])
+//   down-sweep  state[l-1][2i] = state[l][i];  state[l-1][2i+1] = apply(node[l-1][2i], state[l][i])
+// Levels 1..5 are handled by one warp per block of 32 leaves (work spread over the whole GPU), the levels
+// above by one CTA per series, the way back down mirrors that.  The state entering the first chunk is zero or
+// a caller-supplied carry (the hand-off point for sharding one series across GPUs).
+#pragma once
+#include "monoids.cuh"
+
+namespace c2b {
+
+constexpr int kMaxLevels = 24;
+constexpr int kWarpLevels = 5;  // 2^5 = 32 leaves per warp block
+
+struct Levels {
+  int nlev;                      // number of levels, count[nlev-1] == 1
+  int64_t count[kMaxLevels];     // nodes per level (level 0 = leaves = chunks per series)
+  int64_t off[kMaxLevels];       // node offset of each level inside one series
+  int64_t total;                 // nodes per series
+};
+
+static inline Levels make_levels(int64_t leaves) {
+  Levels lv;
+  memset(&lv, 0, sizeof(lv));
+  int l       = 0;
+  int64_t cnt = leaves, off = 0;
+  for (;;) {
+    lv.count[l] = cnt;
+    lv.off[l]   = off;
+    off += cnt;
+    ++l;
+    if (cnt == 1) break;
+    cnt = (cnt + 1) / 2;
+  }
+  lv.nlev  = l;
+  lv.total = off;
+  return lv;
+}
+
+template <class Mon>
+C2B_DEV void up_node(int J, int K, const Levels &lv, double *nodes, int es, int l, int64_t idx) {
+  const double *left = nodes + (lv.off[l - 1] + 2 * idx) * es;
+  double *out        = nodes + (lv.off[l] + idx) * es;
+  if (2 * idx + 1 < lv.count[l - 1]) {
+    Mon::combine(J, K, left, left + es, out);
+  } else {
+    for (int i = 0; i < es; ++i) out[i] = left[i];
+  }
+}
+
+template <class Mon>
+C2B_DEV void down_node(int J, int K, const Levels &lv, const double *nodes, double *states, int es, int ss, int l, int64_t idx) {
+  const double *sin = states + (lv.off[l] + idx) * ss;
+  double *s0        = states + (lv.off[l - 1] + 2 * idx) * ss;
+  for (int i = 0; i < ss; ++i) s0[i] = sin[i];
+  if (2 * idx + 1 < lv.count[l - 1]) Mon::apply(J, K, nodes + (lv.off[l - 1] + 2 * idx) * es, sin, s0 + ss);
+}
+
+// one warp per (series, block of 32 leaves): levels 1..min(5, top)
+template <class Mon>
+__global__ void scan_up_warp(int J, int K, int64_t batch, Levels lv, double *nodes_all) {
+  const int64_t nblk = (lv.count[0] + 31) / 32;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane     = threadIdx.x & 31;
+  if (warp >= batch * nblk) return;
+  const int64_t b = warp / nblk, blk = warp % nblk;
+  const int es  = Mon::esize(J, K);
+  double *nodes = nodes_all + b * lv.total * es;
+  const int top = lv.nlev - 1 < kWarpLevels ? lv.nlev - 1 : kWarpLevels;
+  for (int l = 1; l <= top; ++l) {
+    const int64_t idx = ((blk * 32) >> l) + lane;
+    if (lane < (32 >> l) && idx < lv.count[l]) up_node<Mon>(J, K, lv, nodes, es, l, idx);
+    __syncwarp();
+  }
+}
+
+// one CTA per series: levels 6..top up, then top..6 down (leaves states at level 5)
+template <class Mon>
+__global__ void scan_top(int J, int K, Levels lv, double *nodes_all, double *states_all, const double *init) {
+  const int64_t b = blockIdx.x;
+  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
+  double *nodes  = nodes_all + b * lv.total * es;
+  double *states = states_all + b * lv.total * ss;
+  const int top  = lv.nlev - 1;
+  for (int l = kWarpLevels + 1; l <= top; ++l) {
+    for (int64_t idx = threadIdx.x; idx < lv.count[l]; idx += blockDim.x) up_node<Mon>(J, K, lv, nodes, es, l, idx);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    double *st = states + lv.off[top] * ss;
+    for (int i = 0; i < ss; ++i) st[i] = init ? init[b * ss + i] : 0.0;
+  }
+  __syncthreads();
+  for (int l = top; l > kWarpLevels; --l) {
+    for (int64_t idx = threadIdx.x; idx < lv.count[l]; idx += blockDim.x) down_node<Mon>(J, K, lv, nodes, states, es, ss, l, idx);
+    __syncthreads();
+  }
+}
+
+// one warp per (series, block of 32 leaves): levels min(5, top)..1 down
+template <class Mon>
+__global__ void scan_down_warp(int J, int K, int64_t batch, Levels lv, const double *nodes_all, double *states_all, const double *init) {
+  const int64_t nblk = (lv.count[0] + 31) / 32;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane     = threadIdx.x & 31;
+  if (warp >= batch * nblk) return;
+  const int64_t b = warp / nblk, blk = warp % nblk;
+  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
+  const double *nodes = nodes_all + b * lv.total * es;
+  double *states      = states_all + b * lv.total * ss;
+  const int top       = lv.nlev - 1 < kWarpLevels ? lv.nlev - 1 : kWarpLevels;
+  if (lv.nlev - 1 <= kWarpLevels) {  // the whole tree lives in this warp: seed the top state here
+    if (lane == 0) {
+      double *st = states + lv.off[top] * ss;
+      for (int i = 0; i < ss; ++i) st[i] = init ? init[b * ss + i] : 0.0;
+    }
+    __syncwarp();
+  }
+  for (int l = top; l >= 1; --l) {
+    const int64_t idx = ((blk * 32) >> l) + lane;
+    if (lane < (32 >> l) && idx < lv.count[l]) down_node<Mon>(J, K, lv, nodes, states, es, ss, l, idx);
+    __syncwarp();
+  }
+}
+
+// Scratch needed by a scan over `leaves` chunks per series.
+template <class Mon>
+static inline void scan_sizes(int J, int K, int64_t batch, int64_t leaves, size_t *node_doubles, size_t *state_doubles) {
+  Levels lv      = make_levels(leaves);
+  *node_doubles  = (size_t)batch * lv.total * Mon::esize(J, K);
+  *state_doubles = (size_t)batch * lv.total * Mon::ssize(J, K);
+}
+
+// Leaves must already be in nodes[b][0..leaves).  On return states[b][i] (i < leaves) is the carry into chunk i.
+template <class Mon>
+static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *nodes, double *states, const double *init,
+                           cudaStream_t stream) {
+  Levels lv          = make_levels(leaves);
+  const int64_t nblk = (leaves + 31) / 32;
+  const int threads  = 128;  // 4 warps
+  const int64_t warps = batch * nblk;
+  const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
+  if (lv.nlev > 1) {
+    scan_up_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes);
+    C2B_CHECK_LAUNCH();
+  }
+  if (lv.nlev - 1 > kWarpLevels) {
+    scan_top<Mon><<<(unsigned)batch, 256, 0, stream>>>(J, K, lv, nodes, states, init);
+    C2B_CHECK_LAUNCH();
+  }
+  scan_down_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes, states, init);
+  C2B_CHECK_LAUNCH();
+  return C2B_OK;
+}
+
+// Finalise a reverse op: add the bt term each chunk owes its neighbour and reduce the per-chunk bc partials in
+// a fixed order (deterministic).  One CTA per series.
+//   descending == true  (lower / factor_rev): chunk k owes bt[n0_k - 1]
+//   descending == false (upper)             : chunk k owes bt[n1_k]
+static __global__ void rev_finalize_kernel(int64_t N, int64_t C, int64_t L, int J, bool descending, const double *bc_part,
+                                    const double *bt_edge, double *bt, double *bc) {
+  const int64_t b = blockIdx.x;
+  for (int64_t k = threadIdx.x; k < C; k += blockDim.x) {
+    const int64_t n0 = k * L, n1 = (n0 + L < N) ? n0 + L : N;
+    const int64_t tgt = descending ? n0 - 1 : n1;
+    if (tgt >= 0 && tgt < N) bt[b * N + tgt] += bt_edge[b * C + k];
+  }
+  // bc[j] = sum over chunks, fixed tree order
+  __shared__ double sh[256];
+  for (int j = 0; j < J; ++j) {
+    double s = 0.0;
+    for (int64_t k = threadIdx.x; k < C; k += blockDim.x) s += bc_part[(b * C + k) * J + j];
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int w = blockDim.x / 2; w > 0; w >>= 1) {
+      if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) bc[b * J + j] = sh[0];
+    __syncthreads();
+  }
+}
+
+}  // namespace c2b

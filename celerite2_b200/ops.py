@@ -1,0 +1,255 @@
+"""Device-level operator API: torch CUDA tensors in, torch CUDA tensors out, zero-copy into the C ABI.
+
+torch is plumbing here (device memory, streams); all arithmetic happens in libcelerite2_b200.so.  Each
+function mirrors one reference operation (names, argument order and meaning as in
+python/celerite2/definitions.json); a leading batch dimension on the per-series arrays selects the batched
+kernels.  Shapes: t (N) or (B,N); c (J) or (B,J); a,d (..,N); U,V,W (..,N,J); Y,Z (..,N,K); S (..,N,J,J)
+(S[n] is the reference's row reshaped, i.e. the TRANSPOSE of the column-major matrix); F (..,N,J*K) flat.
+"""
+import torch
+
+from . import _lib
+from ._lib import SHARED_C, SHARED_T, SHARED_Y, check, lib
+
+_scratch = {}
+
+
+def _ptr(x):
+    return None if x is None else x.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _get_scratch(op, N, M, J, K, batch, device):
+    need = lib.c2b_scratch_bytes(_lib.OP_IDS[op], N, M, J, K, batch)
+    if need == 0:
+        return None, 0
+    key = (device.index if device.index is not None else torch.cuda.current_device())
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf.data_ptr(), buf.numel()
+
+
+def _f64(x, name):
+    if not (isinstance(x, torch.Tensor) and x.is_cuda):
+        raise TypeError("%s must be a CUDA tensor" % name)
+    if x.dtype != torch.float64:
+        raise TypeError("%s must be float64 (got %s)" % (name, x.dtype))
+    return x if x.is_contiguous() else x.contiguous()
+
+
+def _batch_of(U):
+    """(batch, N, J) from a (N,J) or (B,N,J) tensor"""
+    if U.dim() == 2:
+        return 1, U.shape[0], U.shape[1]
+    if U.dim() == 3:
+        return U.shape[0], U.shape[1], U.shape[2]
+    raise ValueError("low-rank matrices must have shape (N,J) or (B,N,J)")
+
+
+def _flags(batch, t, c, Y=None):
+    f = 0
+    if t.dim() == 1:
+        f |= SHARED_T
+    if c.dim() == 1:
+        f |= SHARED_C
+    if Y is not None and batch > 1 and Y.dim() == 2:
+        f |= SHARED_Y
+    return f
+
+
+def set_chunks_per_series(chunks):
+    """Force the number of chunks each series is cut into (0 = heuristic).  Testing / tuning knob."""
+    lib.c2b_set_chunks_per_series(int(chunks))
+
+
+# ---- assembly ------------------------------------------------------------------------------------------------
+def get_celerite_matrices(ar, cr, ac, bc, cc, dc, x, diag, layout="blocked"):
+    """-> (c, a, U, V).  Coefficient vectors (Jr,)/(Jc,) or (B,Jr)/(B,Jc); x (N) or (B,N); diag (N) or (B,N)."""
+    ar, cr, ac, bc, cc, dc, x, diag = [_f64(v, n) for v, n in zip((ar, cr, ac, bc, cc, dc, x, diag), "ar cr ac bc cc dc x diag".split())]
+    batch = diag.shape[0] if diag.dim() == 2 else 1
+    N = diag.shape[-1]
+    Jr, Jc = ar.shape[-1], ac.shape[-1]
+    J = Jr + 2 * Jc
+    flags = (SHARED_T if x.dim() == 1 else 0) | (SHARED_C if ar.dim() == 1 and ac.dim() == 1 else 0)
+    lead = (batch,) if diag.dim() == 2 else ()
+    dev = diag.device
+    c = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
+    a = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
+    U = torch.empty(lead + (N, J), dtype=torch.float64, device=dev)
+    V = torch.empty(lead + (N, J), dtype=torch.float64, device=dev)
+    check(lib.c2b_get_celerite_matrices({"blocked": 0, "interleaved": 1}[layout], N, Jr, Jc, batch, _ptr(ar), _ptr(cr), _ptr(ac),
+                                        _ptr(bc), _ptr(cc), _ptr(dc), _ptr(x), _ptr(diag), _ptr(c), _ptr(a), _ptr(U), _ptr(V), flags,
+                                        _stream()))
+    return c, a, U, V
+
+
+def get_celerite_matrices_rev(ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V, b_x=None, layout="blocked", want_diag=True):
+    """Adjoint of the assembly -> (b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_diag).  b_x (if given) is accumulated into."""
+    ar, cr, ac, bc, cc, dc, x, b_a, b_U, b_V = [_f64(v, "arg") for v in (ar, cr, ac, bc, cc, dc, x, b_a, b_U, b_V)]
+    batch = b_a.shape[0] if b_a.dim() == 2 else 1
+    N = b_a.shape[-1]
+    Jr, Jc = ar.shape[-1], ac.shape[-1]
+    flags = (SHARED_T if x.dim() == 1 else 0) | (SHARED_C if ar.dim() == 1 and ac.dim() == 1 else 0)
+    lead = (batch,) if b_a.dim() == 2 else ()
+    dev = b_a.device
+    new = lambda n: torch.empty(lead + (n,), dtype=torch.float64, device=dev)
+    b_ar, b_cr, b_ac, b_bc, b_cc, b_dc = new(Jr), new(Jr), new(Jc), new(Jc), new(Jc), new(Jc)
+    if b_x is None:
+        b_x = torch.zeros(lead + (N,), dtype=torch.float64, device=dev)
+    b_diag = new(N) if want_diag else None
+    sp, sb = _get_scratch("assemble_rev", N, 0, Jr + 2 * Jc, 1, batch, dev)
+    check(lib.c2b_get_celerite_matrices_rev({"blocked": 0, "interleaved": 1}[layout], N, Jr, Jc, batch, _ptr(ar), _ptr(cr), _ptr(ac),
+                                            _ptr(bc), _ptr(cc), _ptr(dc), _ptr(x), _ptr(b_c), _ptr(b_a), _ptr(b_U), _ptr(b_V),
+                                            _ptr(b_ar), _ptr(b_cr), _ptr(b_ac), _ptr(b_bc), _ptr(b_cc), _ptr(b_dc), _ptr(b_x),
+                                            _ptr(b_diag), flags, sp, sb, _stream()))
+    return b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_diag
+
+
+# ---- factor --------------------------------------------------------------------------------------------------
+def factor(t, c, a, U, V, d=None, W=None, workspace=True, status=None):
+    """-> (d, W, S, status).  d / W default to fresh tensors; pass d=a, W=V for the in-place form.
+    status is an int64 tensor (batch): 0 or the first row with a non-positive pivot."""
+    t, c, a, U, V = [_f64(v, n) for v, n in zip((t, c, a, U, V), "tcaUV")]
+    batch, N, J = _batch_of(U)
+    dev = U.device
+    d = torch.empty_like(a) if d is None else d
+    W = torch.empty_like(V) if W is None else W
+    S = torch.empty(U.shape[:-1] + (J, J), dtype=torch.float64, device=dev) if workspace else None
+    status = torch.empty(batch, dtype=torch.int64, device=dev) if status is None else status
+    sp, sb = _get_scratch("factor", N, 0, J, 1, batch, dev)
+    check(lib.c2b_factor(N, J, batch, _ptr(t), _ptr(c), _ptr(a), _ptr(U), _ptr(V), _ptr(d), _ptr(W), _ptr(S), _ptr(status),
+                         _flags(batch, t, c), sp, sb, _stream()))
+    return d, W, S, status
+
+
+def factor_rev(t, c, a, U, V, d, W, S, bd, bW):
+    """-> (bt, bc, ba, bU, bV)"""
+    t, c, U, d, W, S, bd, bW = [_f64(v, "arg") for v in (t, c, U, d, W, S, bd, bW)]
+    batch, N, J = _batch_of(U)
+    dev = U.device
+    lead = U.shape[:-2]
+    bt = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
+    bc = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
+    ba = torch.empty_like(bt)
+    bU, bV = torch.empty_like(U), torch.empty_like(U)
+    sp, sb = _get_scratch("factor_rev", N, 0, J, 1, batch, dev)
+    check(lib.c2b_factor_rev(N, J, batch, _ptr(t), _ptr(c), _ptr(a), _ptr(U), _ptr(V), _ptr(d), _ptr(W), _ptr(S), _ptr(bd), _ptr(bW),
+                             _ptr(bt), _ptr(bc), _ptr(ba), _ptr(bU), _ptr(bV), _flags(batch, t, c), sp, sb, _stream()))
+    return bt, bc, ba, bU, bV
+
+
+# ---- sweeps --------------------------------------------------------------------------------------------------
+def _sweep(op, t, c, U, W, Y, Z, workspace):
+    t, c, U, W, Y = [_f64(v, n) for v, n in zip((t, c, U, W, Y), "tcUWY")]
+    batch, N, J = _batch_of(U)
+    K = Y.shape[-1]
+    dev = U.device
+    solve = op.startswith("solve")
+    if Z is None:
+        Z = torch.empty(U.shape[:-1] + (K,), dtype=torch.float64, device=dev) if solve else torch.zeros(
+            U.shape[:-1] + (K,), dtype=torch.float64, device=dev)
+    F = torch.empty(U.shape[:-1] + (J * K,), dtype=torch.float64, device=dev) if workspace else None
+    sp, sb = _get_scratch(op, N, 0, J, K, batch, dev)
+    fn = getattr(lib, "c2b_" + op)
+    check(fn(N, J, K, batch, _ptr(t), _ptr(c), _ptr(U), _ptr(W), _ptr(Y), _ptr(Z), _ptr(F), _flags(batch, t, c, Y), sp, sb, _stream()))
+    return Z, F
+
+
+def solve_lower(t, c, U, W, Y, Z=None, workspace=False):
+    """Z = L^-1 Y -> (Z, F).  Pass Z=Y for the in-place form."""
+    return _sweep("solve_lower", t, c, U, W, Y, Z, workspace)
+
+
+def solve_upper(t, c, U, W, Y, Z=None, workspace=False):
+    return _sweep("solve_upper", t, c, U, W, Y, Z, workspace)
+
+
+def matmul_lower(t, c, U, V, Y, Z=None, workspace=False):
+    """Z += tril(U V^T) Y (Z defaults to zeros) -> (Z, F)"""
+    return _sweep("matmul_lower", t, c, U, V, Y, Z, workspace)
+
+
+def matmul_upper(t, c, U, V, Y, Z=None, workspace=False):
+    return _sweep("matmul_upper", t, c, U, V, Y, Z, workspace)
+
+
+def _sweep_rev(op, t, c, U, W, Y, Z, F, bZ):
+    t, c, U, W, Y, Z, F, bZ = [_f64(v, "arg") for v in (t, c, U, W, Y, Z, F, bZ)]
+    batch, N, J = _batch_of(U)
+    K = Z.shape[-1]
+    dev = U.device
+    lead = U.shape[:-2]
+    bt = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
+    bc = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
+    bU, bW = torch.empty_like(U), torch.empty_like(U)
+    bY = torch.empty_like(Z)
+    sp, sb = _get_scratch(op, N, 0, J, K, batch, dev)
+    fn = getattr(lib, "c2b_" + op)
+    check(fn(N, J, K, batch, _ptr(t), _ptr(c), _ptr(U), _ptr(W), _ptr(Y), _ptr(Z), _ptr(F), _ptr(bZ), _ptr(bt), _ptr(bc), _ptr(bU),
+             _ptr(bW), _ptr(bY), _flags(batch, t, c, Y), sp, sb, _stream()))
+    return bt, bc, bU, bW, bY
+
+
+def solve_lower_rev(t, c, U, W, Y, Z, F, bZ):
+    """-> (bt, bc, bU, bW, bY)"""
+    return _sweep_rev("solve_lower_rev", t, c, U, W, Y, Z, F, bZ)
+
+
+def solve_upper_rev(t, c, U, W, Y, Z, F, bZ):
+    return _sweep_rev("solve_upper_rev", t, c, U, W, Y, Z, F, bZ)
+
+
+def matmul_lower_rev(t, c, U, V, Y, Z, F, bZ):
+    return _sweep_rev("matmul_lower_rev", t, c, U, V, Y, Z, F, bZ)
+
+
+def matmul_upper_rev(t, c, U, V, Y, Z, F, bZ):
+    return _sweep_rev("matmul_upper_rev", t, c, U, V, Y, Z, F, bZ)
+
+
+# ---- rectangular products ------------------------------------------------------------------------------------
+def _general_matmul(upper, t1, t2, c, U, V, Y, Z, F):
+    t1, t2, c, U, V, Y = [_f64(v, "arg") for v in (t1, t2, c, U, V, Y)]
+    N, M, J, K = t1.shape[0], t2.shape[0], c.shape[0], Y.shape[1]
+    dev = U.device
+    if Z is None:
+        Z = torch.zeros((N, K), dtype=torch.float64, device=dev)
+    sp, sb = _get_scratch("general_matmul", N, M, J, K, 1, dev)
+    fn = lib.c2b_general_matmul_upper if upper else lib.c2b_general_matmul_lower
+    check(fn(N, M, J, K, _ptr(t1), _ptr(t2), _ptr(c), _ptr(U), _ptr(V), _ptr(Y), _ptr(Z), _ptr(F), sp, sb, _stream()))
+    return Z
+
+
+def general_matmul_lower(t1, t2, c, U, V, Y, Z=None, F=None):
+    return _general_matmul(False, t1, t2, c, U, V, Y, Z, F)
+
+
+def general_matmul_upper(t1, t2, c, U, V, Y, Z=None, F=None):
+    return _general_matmul(True, t1, t2, c, U, V, Y, Z, F)
+
+
+# ---- reductions ----------------------------------------------------------------------------------------------
+def norm_logdet(d, z, want_grad=False):
+    """-> (out, bz, bd): out[..., 0] = sum log d, out[..., 1] = sum z^2/d; bz, bd seed the backward pass of
+    loglike = -0.5 (chi2 + logdet + N log 2 pi) when want_grad."""
+    d, z = _f64(d, "d"), _f64(z, "z")
+    batch = d.shape[0] if d.dim() == 2 else 1
+    N = d.shape[-1]
+    dev = d.device
+    out = torch.empty(d.shape[:-1] + (2,), dtype=torch.float64, device=dev)
+    bz = torch.empty_like(z) if want_grad else None
+    bd = torch.empty_like(d) if want_grad else None
+    need = 256 * 1024
+    key = ("red", dev.index)
+    buf = _scratch.get(key)
+    need = max(need, batch * 592 * 16 + 256)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.uint8, device=dev)
+        _scratch[key] = buf
+    check(lib.c2b_norm_logdet(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(bz), _ptr(bd), buf.data_ptr(), buf.numel(), _stream()))
+    return out, bz, bd

@@ -1,0 +1,190 @@
+/*
+ * celerite2_b200 -- C ABI of the B200-native semiseparable Gaussian-process core.
+ *
+ * One entry point per operation of the reference's hot path.  Each comment names
+ * the reference interface the entry point replaces (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer to FP64, C-contiguous, batch-major:
+ *       t (batch,N) | c (batch,J) | a,d (batch,N) | U,V,W (batch,N,J) | Y,Z (batch,N,K)
+ *       S (batch,N,J*J)  row n = column-major J x J   (c++/include/celerite2/forward.hpp:97-103,116-120)
+ *       F (batch,N,J*K)  row n = column-major J x K   (c++/include/celerite2/internal.hpp:127-129)
+ *     `flags` may drop the batch dimension of t, c or Y (C2B_SHARED_*): one array shared by all series.
+ *   - batch == 1 is the reference's single-series call.
+ *   - calls are asynchronous on `stream` (a cudaStream_t passed as void*; NULL = default stream).
+ *   - `scratch`: chunked-scan workspace in device memory.  Ask c2b_scratch_bytes() for the size; pass a
+ *     buffer of at least that many bytes (256-byte aligned), or NULL to let the library allocate and free
+ *     one around the call with cudaMallocAsync/cudaFreeAsync on `stream`.
+ *   - return value: 0 on success, a negative C2B_ERR_* code otherwise (text via c2b_last_error()).
+ *     Nothing here synchronises the device; numerical failure of `factor` is reported through the
+ *     device-side `status` array, exactly one int64 per series (see c2b_factor).
+ *   - supported widths: 1 <= J <= 32 (compiled fast paths for J = 1..8 and 16), any K >= 1, any N >= 1.
+ */
+#ifndef CELERITE2_B200_H_
+#define CELERITE2_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define C2B_OK 0
+#define C2B_ERR_INVALID_ARGUMENT (-1) /* bad size / null pointer / unsupported width */
+#define C2B_ERR_SCRATCH_TOO_SMALL (-2)
+#define C2B_ERR_CUDA (-3) /* a CUDA runtime call failed; see c2b_last_error() */
+#define C2B_ERR_NO_DEVICE (-4)
+
+#define C2B_SHARED_T 1 /* t has shape (N) for all series          */
+#define C2B_SHARED_C 2 /* c (and the coefficient vectors of the assembly) are shared */
+#define C2B_SHARED_Y 4 /* Y (or y) has no batch dimension          */
+
+#define C2B_MAX_J 32
+
+/* Operation ids for c2b_scratch_bytes */
+enum c2b_op {
+  C2B_OP_FACTOR           = 0,
+  C2B_OP_FACTOR_REV       = 1,
+  C2B_OP_SOLVE_LOWER      = 2,
+  C2B_OP_SOLVE_UPPER      = 3,
+  C2B_OP_MATMUL_LOWER     = 4,
+  C2B_OP_MATMUL_UPPER     = 5,
+  C2B_OP_SOLVE_LOWER_REV  = 6,
+  C2B_OP_SOLVE_UPPER_REV  = 7,
+  C2B_OP_MATMUL_LOWER_REV = 8,
+  C2B_OP_MATMUL_UPPER_REV = 9,
+  C2B_OP_GENERAL_MATMUL   = 10,
+  C2B_OP_ASSEMBLE_REV     = 11
+};
+
+const char *c2b_version(void);
+/* Text of the last error on the calling thread ("" if none). */
+const char *c2b_last_error(void);
+/* Number of CUDA devices visible to the library (0 => every compute call fails with C2B_ERR_NO_DEVICE). */
+int32_t c2b_device_count(void);
+/* Bytes of scratch the given operation needs for these sizes (M only matters for GENERAL_MATMUL). */
+size_t c2b_scratch_bytes(int32_t op, int64_t N, int64_t M, int32_t J, int32_t K, int64_t batch);
+/* Override the chunk planner (testing / tuning): chunks per series; 0 restores the heuristic. */
+void c2b_set_chunks_per_series(int64_t chunks);
+
+/*
+ * a/U/V (and c) assembly from the kernel coefficients.
+ *   layout 0 "blocked"     [real.. | cos.. | sin..]       replaces celerite2::Term::get_celerite_matrices,
+ *                                                         c++/include/celerite2/terms.hpp:112-139
+ *   layout 1 "interleaved" [real.. | cos0 sin0 cos1 ..]   replaces driver.get_celerite_matrices,
+ *                                                         python/celerite2/driver.cpp:422-477 (+ c fill, terms.py:171-173)
+ * ar,cr (batch,Jr)  ac,bc,cc,dc (batch,Jc)  x,diag (batch,N)  ->  c (batch,J)  a (batch,N)  U,V (batch,N,J),
+ * J = Jr + 2 Jc.  c_out may be NULL.  C2B_SHARED_T: x shared; C2B_SHARED_C: coefficient vectors shared.
+ */
+int c2b_get_celerite_matrices(int32_t layout, int64_t N, int32_t Jr, int32_t Jc, int64_t batch, const double *ar, const double *cr,
+                              const double *ac, const double *bc, const double *cc, const double *dc, const double *x,
+                              const double *diag, double *c_out, double *a_out, double *U_out, double *V_out, int32_t flags,
+                              void *stream);
+
+/*
+ * Adjoint of the assembly: cotangents of (c, a, U, V) -> cotangents of the six coefficient vectors, of x and
+ * of diag.  The reference has no C++ counterpart: JAX differentiates python/celerite2/jax/terms.py:119-135
+ * itself; this kernel is that derivative written out.  b_c may be NULL (treated as zero).  b_x / b_diag may be
+ * NULL.  b_x is ACCUMULATED into (so the caller can pre-load the `bt` of the sweeps); everything else is overwritten.
+ * Coefficient cotangents have shape (batch,Jr) / (batch,Jc) even when the coefficients are shared.
+ */
+int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t Jc, int64_t batch, const double *ar, const double *cr,
+                                  const double *ac, const double *bc, const double *cc, const double *dc, const double *x,
+                                  const double *b_c, const double *b_a, const double *b_U, const double *b_V, double *b_ar,
+                                  double *b_cr, double *b_ac, double *b_bc, double *b_cc, double *b_dc, double *b_x, double *b_diag,
+                                  int32_t flags, void *scratch, size_t scratch_bytes, void *stream);
+
+/*
+ * LDL^T factorisation.  Replaces celerite2::core::factor, c++/include/celerite2/forward.hpp:69-135
+ * (S != NULL) and the no-workspace overload c++/include/celerite2/interface.hpp:37-48 (S == NULL).
+ * d may alias a and W may alias V (forward.hpp:55-58).
+ * status (batch int64, may be NULL): 0, or the first n >= 1 with d[n] <= 0 (forward.hpp:128).  When a
+ * series runs as ONE chunk (always the case for N below the chunking threshold) rows after that index are
+ * left untouched, as in the reference; when it runs chunked, rows after it hold unspecified values.
+ */
+int c2b_factor(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U,
+               const double *V, double *d, double *W, double *S, int64_t *status, int32_t flags, void *scratch,
+               size_t scratch_bytes, void *stream);
+
+/*
+ * Reverse mode of factor.  Replaces celerite2::core::factor_rev, c++/include/celerite2/reverse.hpp:10-85.
+ * a and V are accepted for signature parity and never read (reverse.hpp:29-30).  All outputs are overwritten.
+ * bc has shape (batch,J) even when c is shared.
+ */
+int c2b_factor_rev(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U,
+                   const double *V, const double *d, const double *W, const double *S, const double *bd, const double *bW,
+                   double *bt, double *bc, double *ba, double *bU, double *bV, int32_t flags, void *scratch,
+                   size_t scratch_bytes, void *stream);
+
+/*
+ * The four linear sweeps.  F may be NULL (the no-workspace overloads, interface.hpp:70-152).  Z may alias Y.
+ *   c2b_solve_lower   Z = L^-1 Y          celerite2::core::solve_lower,  forward.hpp:156-170 -> internal.hpp:105-146
+ *   c2b_solve_upper   Z = L^-T Y          celerite2::core::solve_upper,  forward.hpp:193-207 -> internal.hpp:148-189
+ *   c2b_matmul_lower  Z += tril(U V^T) Y  celerite2::core::matmul_lower, forward.hpp:228-239 (Z is accumulated into)
+ *   c2b_matmul_upper  Z += triu(V U^T) Y  celerite2::core::matmul_upper, forward.hpp:260-271 (Z is accumulated into)
+ */
+int c2b_solve_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                    const double *W, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                    void *stream);
+int c2b_solve_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                    const double *W, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                    void *stream);
+int c2b_matmul_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                     const double *V, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                     void *stream);
+int c2b_matmul_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                     const double *V, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                     void *stream);
+
+/*
+ * Reverse mode of the sweeps.  Replace celerite2::core::{solve_lower,solve_upper,matmul_lower,matmul_upper}_rev,
+ * c++/include/celerite2/reverse.hpp:87-217 -> internal.hpp:191-303.  All outputs are overwritten.
+ * bc has shape (batch,J); bY has shape (batch,N,K) even when Y is shared.
+ */
+int c2b_solve_lower_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                        const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                        double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                        void *stream);
+int c2b_solve_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                        const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                        double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                        void *stream);
+int c2b_matmul_lower_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                         const double *V, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                         double *bc, double *bU, double *bV, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                         void *stream);
+int c2b_matmul_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                         const double *V, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                         double *bc, double *bU, double *bV, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                         void *stream);
+
+/*
+ * Rectangular products used by predict / conditional means.  Replace celerite2::core::general_matmul_lower,
+ * c++/include/celerite2/forward.hpp:285-332 and general_matmul_upper, forward.hpp:346-392.
+ * t1 (N)  t2 (M)  c (J)  U (N,J)  V (M,J)  Y (M,K)  ->  Z (N,K) accumulated into.  Single series (no batch).
+ * F (M,J*K, ROW-major rows, forward.hpp:299) may be NULL; when given, the rows the reference writes hold the
+ * reference's values and row 0 follows forward.hpp:307,369; other rows are left untouched.
+ */
+int c2b_general_matmul_lower(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
+                             const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
+                             size_t scratch_bytes, void *stream);
+int c2b_general_matmul_upper(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
+                             const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
+                             size_t scratch_bytes, void *stream);
+
+/*
+ * The elementwise/reduction glue of the reference's Python layer, fused:
+ *   logdet = sum log d                      python/celerite2/numpy.py:84
+ *   chi2   = sum z^2 / d                    python/celerite2/numpy.py:104-109
+ * out (batch,2) = {logdet, chi2}.  If bz / bd are non-NULL they receive the cotangents of
+ * loglike = -0.5 (chi2 + logdet + N log 2 pi):  bz = -z/d,  bd = 0.5 z^2/d^2 - 0.5/d.
+ * d (batch,N), z (batch,N).
+ */
+int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd,
+                    void *scratch, size_t scratch_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CELERITE2_B200_H_ */
