@@ -3,10 +3,10 @@
 `ops`      device-level operators on torch CUDA tensors (zero-copy into the C ABI)
 `driver`   host mirror of the reference's `celerite2.driver` module (numpy in / numpy out)
 `backprop` host mirror of the reference's `celerite2.backprop` module
-`gp`       fused log-likelihood (+ gradient) pipelines built from the operators
+`gp`       log-likelihood (+ gradient) pipelines built from the operators
+`workloads` synthetic kernels / light curves of the benchmark configurations
 
-Importing the package loads celerite2_b200/libcelerite2_b200.so and fails loudly if it is missing.
+Importing any compute submodule loads celerite2_b200/libcelerite2_b200.so and fails loudly if it is
+missing (build it with `python -m celerite2_b200.build`); there is no CPU fallback.
 """
-from ._lib import C2BError, lib, version  # noqa: F401
-
 __version__ = "0.1.0"

@@ -30,12 +30,14 @@ _SIGS = {
     "c2b_general_matmul_lower": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
+    "c2b_add_inplace": [_i64, _vp, _vp, _vp],
 }
 for _op in ("solve_lower", "solve_upper", "matmul_lower", "matmul_upper"):
     _SIGS["c2b_" + _op] = [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp]
     _SIGS["c2b_" + _op + "_rev"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp]
 
-EXPORTS = sorted(list(_SIGS) + ["c2b_version", "c2b_last_error", "c2b_device_count", "c2b_scratch_bytes", "c2b_set_chunks_per_series"])
+EXPORTS = sorted(list(_SIGS) + ["c2b_version", "c2b_last_error", "c2b_device_count", "c2b_scratch_bytes", "c2b_set_chunks_per_series",
+                                 "c2b_profile_enable", "c2b_profile_report"])
 
 
 class C2BError(RuntimeError):
@@ -61,6 +63,10 @@ def _load():
     lib.c2b_device_count.argtypes = []
     lib.c2b_scratch_bytes.restype = _sz
     lib.c2b_scratch_bytes.argtypes = [_i32, _i64, _i64, _i32, _i32, _i64]
+    lib.c2b_profile_enable.restype = None
+    lib.c2b_profile_enable.argtypes = [_i32]
+    lib.c2b_profile_report.restype = ctypes.c_char_p
+    lib.c2b_profile_report.argtypes = []
     lib.c2b_set_chunks_per_series.restype = None
     lib.c2b_set_chunks_per_series.argtypes = [_i64]
     return lib

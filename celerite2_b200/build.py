@@ -30,8 +30,18 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
 
-def _sources():
-    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC))] + [os.path.join(HERE, "..", "include", "celerite2_b200.h")]
+_COMMON = ["common.cuh", "monoids.cuh", "scan.cuh", "args.cuh", "host_common.cuh"]
+_EXTRA = {
+    "api_misc.cu": ["misc.cuh"],
+    "api_pipeline.cu": ["misc.cuh"],
+    "inst_sweep.cu": ["sweep.cuh"],
+    "inst_factor.cu": ["factor.cuh"],
+}
+
+
+def _deps(unit):
+    files = [unit] + _COMMON + _EXTRA.get(unit, [])
+    return [os.path.join(CSRC, f) for f in files] + [os.path.join(HERE, "..", "include", "celerite2_b200.h")]
 
 
 def _stale(target, deps):
@@ -43,7 +53,6 @@ def _stale(target, deps):
 
 def build(force=False, verbose_ptxas=False):
     os.makedirs(OBJ, exist_ok=True)
-    deps = _sources()
     units = [(u, w) for (u, w) in UNITS if os.path.exists(os.path.join(CSRC, u))]
 
     def objname(u, w):
@@ -52,7 +61,7 @@ def build(force=False, verbose_ptxas=False):
     jobs = []
     for u, w in units:
         obj = objname(u, w)
-        if force or _stale(obj, deps):
+        if force or _stale(obj, _deps(u)):
             cmd = [NVCC] + ARCH + FLAGS + (["-Xptxas", "-v"] if verbose_ptxas else [])
             if w is not None:
                 cmd += ["-DC2B_JT=%d" % w]

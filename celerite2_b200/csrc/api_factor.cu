@@ -38,6 +38,7 @@ extern "C" {
 
 int c2b_factor(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U, const double *V,
                double *d, double *W, double *S, int64_t *status, int32_t flags, void *scratch, size_t scratch_bytes, void *stream_) {
+  c2b::OpScope _op("c2b_factor");
   using namespace c2b;
   int rc = check_common(N, J, batch);
   if (rc) return rc;
@@ -68,6 +69,7 @@ int c2b_factor(int64_t N, int32_t J, int64_t batch, const double *t, const doubl
 int c2b_factor_rev(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U,
                    const double *V, const double *d, const double *W, const double *S, const double *bd, const double *bW, double *bt,
                    double *bc, double *ba, double *bU, double *bV, int32_t flags, void *scratch, size_t scratch_bytes, void *stream_) {
+  c2b::OpScope _op("c2b_factor_rev");
   using namespace c2b;
   (void)a;
   (void)V;

@@ -2,6 +2,11 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
 #include "host_common.cuh"
 #include "misc.cuh"
 
@@ -9,6 +14,39 @@ namespace c2b {
 
 static thread_local char g_err[512] = "";
 static int64_t g_chunk_override    = -1;  // -1: not yet read from the environment
+
+bool g_profile_on               = false;
+thread_local const char *g_op   = "";
+namespace {
+struct ProfRec {
+  const char *op, *kernel;
+  cudaEvent_t e0, e1;
+};
+std::vector<ProfRec> g_recs;
+std::vector<cudaEvent_t> g_event_pool;
+std::mutex g_prof_mutex;
+std::string g_report;
+cudaEvent_t get_event() {
+  if (!g_event_pool.empty()) {
+    cudaEvent_t e = g_event_pool.back();
+    g_event_pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e;
+  cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+void prof_begin(const char *kernel, cudaStream_t s) {
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  ProfRec r{g_op, kernel, get_event(), get_event()};
+  cudaEventRecord(r.e0, s);
+  g_recs.push_back(r);
+}
+void prof_end(cudaStream_t s) {
+  std::lock_guard<std::mutex> lock(g_prof_mutex);
+  if (!g_recs.empty()) cudaEventRecord(g_recs.back().e1, s);
+}
 
 void set_error(const char *fmt, ...) {
   va_list ap;
@@ -129,19 +167,15 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
   if (pl.C > 1) {
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
-    gm_scan_kernel<UPPER, true><<<grid, block, 0, stream>>>(g);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, true><<<grid, block, 0, stream>>>(g));
     rc = run_scan<DiagV<0>>(J, K, 1, pl.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
-  gm_scan_kernel<UPPER, false><<<grid, block, 0, stream>>>(g);
-  C2B_CHECK_LAUNCH();
-  gm_gather_kernel<UPPER><<<(unsigned)((N * K + 127) / 128), 128, 0, stream>>>(g);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, false><<<grid, block, 0, stream>>>(g));
+  C2B_LAUNCH("gm_gather_kernel", stream, gm_gather_kernel<UPPER><<<(unsigned)((N * K + 127) / 128), 128, 0, stream>>>(g));
   if (F) {
-    gm_workspace_kernel<UPPER><<<(unsigned)((M * (int64_t)J * K + 127) / 128), 128, 0, stream>>>(g);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("gm_workspace_kernel", stream, gm_workspace_kernel<UPPER><<<(unsigned)((M * (int64_t)J * K + 127) / 128), 128, 0, stream>>>(g));
   }
   return C2B_OK;
 }
@@ -160,6 +194,38 @@ int32_t c2b_device_count(void) {
     return 0;
   }
   return n;
+}
+
+void c2b_profile_enable(int32_t on) {
+  std::lock_guard<std::mutex> lock(c2b::g_prof_mutex);
+  for (auto &r : c2b::g_recs) {
+    c2b::g_event_pool.push_back(r.e0);
+    c2b::g_event_pool.push_back(r.e1);
+  }
+  c2b::g_recs.clear();
+  c2b::g_profile_on = on != 0;
+}
+
+const char *c2b_profile_report(void) {
+  std::lock_guard<std::mutex> lock(c2b::g_prof_mutex);
+  std::map<std::string, std::pair<long, double>> agg;
+  std::vector<std::string> order;
+  for (auto &r : c2b::g_recs) {
+    if (cudaEventSynchronize(r.e1) != cudaSuccess) continue;
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.e0, r.e1) != cudaSuccess) continue;
+    std::string key = std::string(r.op) + "/" + r.kernel;
+    if (!agg.count(key)) order.push_back(key);
+    agg[key].first += 1;
+    agg[key].second += ms;
+  }
+  c2b::g_report.clear();
+  char buf[256];
+  for (auto &k : order) {
+    snprintf(buf, sizeof(buf), "%s %ld %.6f\n", k.c_str(), agg[k].first, agg[k].second);
+    c2b::g_report += buf;
+  }
+  return c2b::g_report.c_str();
 }
 
 void c2b_set_chunks_per_series(int64_t chunks) { c2b::g_chunk_override = chunks > 0 ? chunks : 0; }
@@ -189,6 +255,7 @@ int c2b_get_celerite_matrices(int32_t layout, int64_t N, int32_t Jr, int32_t Jc,
                               const double *ac, const double *bc, const double *cc, const double *dc, const double *x,
                               const double *diag, double *c_out, double *a_out, double *U_out, double *V_out, int32_t flags,
                               void *stream_) {
+  c2b::OpScope _op("c2b_get_celerite_matrices");
   using namespace c2b;
   C2B_REQUIRE(Jr >= 0 && Jc >= 0, "negative term count");
   int rc = check_common(N, Jr + 2 * Jc, batch);
@@ -205,8 +272,7 @@ int c2b_get_celerite_matrices(int32_t layout, int64_t N, int32_t Jr, int32_t Jc,
   g.co_r_bs = (flags & C2B_SHARED_C) ? 0 : Jr;
   g.co_c_bs = (flags & C2B_SHARED_C) ? 0 : Jc;
   const int64_t total = batch * N;
-  assemble_kernel<<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream_>>>(g);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("assemble_kernel", (cudaStream_t)stream_, assemble_kernel<<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream_>>>(g));
   return C2B_OK;
 }
 
@@ -215,6 +281,7 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
                                   const double *b_c, const double *b_a, const double *b_U, const double *b_V, double *b_ar,
                                   double *b_cr, double *b_ac, double *b_bc, double *b_cc, double *b_dc, double *b_x, double *b_diag,
                                   int32_t flags, void *scratch, size_t scratch_bytes, void *stream_) {
+  c2b::OpScope _op("c2b_get_celerite_matrices_rev");
   using namespace c2b;
   (void)cr;
   (void)cc;
@@ -242,15 +309,14 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
   g.ctas_per_series = asm_rev_ctas(N);
   const int nred    = Jr + 3 * Jc;
   dim3 grid((unsigned)g.ctas_per_series, (unsigned)batch);
-  assemble_rev_kernel<<<grid, kAsmRevThreads, (size_t)nred * kAsmRevThreads * sizeof(double), stream>>>(g);
-  C2B_CHECK_LAUNCH();
-  assemble_rev_final_kernel<<<(unsigned)batch, 64, 0, stream>>>(g);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("assemble_rev_kernel", stream, assemble_rev_kernel<<<grid, kAsmRevThreads, (size_t)nred * kAsmRevThreads * sizeof(double), stream>>>(g));
+  C2B_LAUNCH("assemble_rev_final_kernel", stream, assemble_rev_final_kernel<<<(unsigned)batch, 64, 0, stream>>>(g));
   return C2B_OK;
 }
 
 int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd, void *scratch,
                     size_t scratch_bytes, void *stream_) {
+  c2b::OpScope _op("c2b_norm_logdet");
   using namespace c2b;
   int rc = check_common(N, 1, batch);
   if (rc) return rc;
@@ -261,21 +327,32 @@ int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, 
   if (rc) return rc;
   const int ctas = red_ctas(N);
   dim3 grid((unsigned)ctas, (unsigned)batch);
-  norm_logdet_kernel<<<grid, kRedThreads, 0, stream>>>(N, d, z, bz, bd, (double *)sc.ptr, ctas);
-  C2B_CHECK_LAUNCH();
-  norm_logdet_final_kernel<<<(unsigned)batch, 32, 0, stream>>>((const double *)sc.ptr, ctas, out);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("norm_logdet_kernel", stream, norm_logdet_kernel<<<grid, kRedThreads, 0, stream>>>(N, d, z, bz, bd, (double *)sc.ptr, ctas));
+  C2B_LAUNCH("norm_logdet_final_kernel", stream, norm_logdet_final_kernel<<<(unsigned)batch, 32, 0, stream>>>((const double *)sc.ptr, ctas, out));
+  return C2B_OK;
+}
+
+int c2b_add_inplace(int64_t n, const double *x, double *y, void *stream_) {
+  c2b::OpScope _op("c2b_add_inplace");
+  using namespace c2b;
+  C2B_REQUIRE(n >= 0 && (n == 0 || (x && y)), "bad arguments");
+  if (n == 0) return C2B_OK;
+  int64_t blocks = (n + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  C2B_LAUNCH("add_inplace_kernel", (cudaStream_t)stream_, add_inplace_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(n, x, y));
   return C2B_OK;
 }
 
 int c2b_general_matmul_lower(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
                              const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
                              size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_general_matmul_lower");
   return c2b::general_matmul_entry<false>(N, M, J, K, t1, t2, c, U, V, Y, Z, F, scratch, scratch_bytes, stream);
 }
 int c2b_general_matmul_upper(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
                              const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
                              size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_general_matmul_upper");
   return c2b::general_matmul_entry<true>(N, M, J, K, t1, t2, c, U, V, Y, Z, F, scratch, scratch_bytes, stream);
 }
 

@@ -123,42 +123,50 @@ extern "C" {
 
 int c2b_solve_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
                     const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_solve_lower");
   return c2b::sweep_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, F, flags, scratch, scratch_bytes, stream);
 }
 int c2b_solve_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
                     const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_solve_upper");
   return c2b::sweep_entry<true, false>(N, J, K, batch, t, c, U, W, Y, Z, F, flags, scratch, scratch_bytes, stream);
 }
 int c2b_matmul_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *V,
                      const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_matmul_lower");
   return c2b::sweep_entry<false, true>(N, J, K, batch, t, c, U, V, Y, Z, F, flags, scratch, scratch_bytes, stream);
 }
 int c2b_matmul_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *V,
                      const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_matmul_upper");
   return c2b::sweep_entry<false, false>(N, J, K, batch, t, c, U, V, Y, Z, F, flags, scratch, scratch_bytes, stream);
 }
 
 int c2b_solve_lower_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
                         const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
                         double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_solve_lower_rev");
   return c2b::sweep_rev_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, F, bZ, bt, bc, bU, bW, bY, flags, scratch, scratch_bytes,
                                           stream);
 }
 int c2b_solve_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
                         const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
                         double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_solve_upper_rev");
   return c2b::sweep_rev_entry<true, false>(N, J, K, batch, t, c, U, W, Y, Z, F, bZ, bt, bc, bU, bW, bY, flags, scratch, scratch_bytes,
                                            stream);
 }
 int c2b_matmul_lower_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
                          const double *V, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
                          double *bU, double *bV, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_matmul_lower_rev");
   return c2b::sweep_rev_entry<false, true>(N, J, K, batch, t, c, U, V, Y, Z, F, bZ, bt, bc, bU, bV, bY, flags, scratch, scratch_bytes,
                                            stream);
 }
 int c2b_matmul_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
                          const double *V, const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc,
                          double *bU, double *bV, double *bY, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_matmul_upper_rev");
   return c2b::sweep_rev_entry<false, false>(N, J, K, batch, t, c, U, V, Y, Z, F, bZ, bt, bc, bU, bV, bY, flags, scratch, scratch_bytes,
                                             stream);
 }

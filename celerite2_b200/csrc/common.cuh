@@ -39,6 +39,26 @@ int cuda_fail(cudaError_t e, const char *what);
     }                                                                                                                                     \
   } while (0)
 
+// ---- built-in kernel timing (bench support) -------------------------------------------------------------------
+// When enabled (c2b_profile_enable) every kernel launch is bracketed by a pair of CUDA events on its stream;
+// c2b_profile_report() turns them into per-(entry point, kernel) totals.
+extern bool g_profile_on;
+extern thread_local const char *g_op;
+void prof_begin(const char *kernel, cudaStream_t s);
+void prof_end(cudaStream_t s);
+struct OpScope {
+  const char *prev;
+  explicit OpScope(const char *name) : prev(g_op) { g_op = name; }
+  ~OpScope() { g_op = prev; }
+};
+#define C2B_LAUNCH(name, stream, ...)                                                                                                     \
+  do {                                                                                                                                    \
+    if (c2b::g_profile_on) c2b::prof_begin(name, stream);                                                                                 \
+    __VA_ARGS__;                                                                                                                          \
+    if (c2b::g_profile_on) c2b::prof_end(stream);                                                                                         \
+    C2B_CHECK_LAUNCH();                                                                                                                   \
+  } while (0)
+
 // ---- chunk plan ---------------------------------------------------------------------------------------------
 // A series of N points is cut into C chunks of L points (the last one shorter).  Chunks are the unit of
 // parallelism along N; carries between chunks come from an associative scan over per-chunk summaries.

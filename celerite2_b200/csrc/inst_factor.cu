@@ -15,14 +15,12 @@ int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
   if (g.C > 1) {
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
-    factor_summary_kernel<JT><<<grid, block, 0, stream>>>(g);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("factor_summary_kernel", stream, factor_summary_kernel<JT><<<grid, block, 0, stream>>>(g));
     int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
-  factor_apply_kernel<JT><<<grid, block, 0, stream>>>(g);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("factor_apply_kernel", stream, factor_apply_kernel<JT><<<grid, block, 0, stream>>>(g));
   return C2B_OK;
 }
 
@@ -33,17 +31,14 @@ int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaS
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
     launch_shape(g.batch * g.C * (g.J + 1), &grid, &block);
-    factor_rev_summary_kernel<JT><<<grid, block, 0, stream>>>(g);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("factor_rev_summary_kernel", stream, factor_rev_summary_kernel<JT><<<grid, block, 0, stream>>>(g));
     int rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
   launch_shape(g.batch * g.C, &grid, &block);
-  factor_rev_apply_kernel<JT><<<grid, block, 0, stream>>>(g);
-  C2B_CHECK_LAUNCH();
-  rev_finalize_kernel<<<(unsigned)g.batch, 256, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("factor_rev_apply_kernel", stream, factor_rev_apply_kernel<JT><<<grid, block, 0, stream>>>(g));
+  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<(unsigned)g.batch, 256, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc));
   return C2B_OK;
 }
 

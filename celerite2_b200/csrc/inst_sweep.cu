@@ -16,8 +16,7 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
     a.node_stride = sb.node_stride;
     const int ncol = SOLVE ? a.J + a.K : a.K;
     launch_shape(a.batch * a.C * ncol, &grid, &block);
-    sweep_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("sweep_summary_kernel", stream, sweep_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
     int rc;
     if (SOLVE)
       rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
@@ -27,8 +26,7 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
     a.carry = sb.states;
   }
   launch_shape(a.batch * a.C * a.K, &grid, &block);
-  sweep_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("sweep_apply_kernel", stream, sweep_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
   return C2B_OK;
 }
 
@@ -40,8 +38,7 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
     a.node_stride = sb.node_stride;
     const int ncol = SOLVE ? a.J + a.K : a.K;
     launch_shape(a.batch * a.C * ncol, &grid, &block);
-    sweep_rev_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("sweep_rev_summary_kernel", stream, sweep_rev_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
     int rc;
     if (SOLVE)
       rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
@@ -51,10 +48,8 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
     a.carry = sb.states;
   }
   launch_shape(a.batch * a.C, &grid, &block);
-  sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a);
-  C2B_CHECK_LAUNCH();
-  rev_finalize_kernel<<<(unsigned)a.batch, 256, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("sweep_rev_apply_kernel", stream, sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
+  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<(unsigned)a.batch, 256, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc));
   return C2B_OK;
 }
 

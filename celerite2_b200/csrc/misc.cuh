@@ -167,6 +167,10 @@ __global__ void norm_logdet_final_kernel(const double *part, int ctas, double *o
   }
 }
 
+__global__ void add_inplace_kernel(int64_t n, const double *x, double *y) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] += x[i];
+}
+
 // ---- general_matmul (forward.hpp:285-392) ------------------------------------------------------------------------
 // Step 1: running state over t2, H_m = P_m H_{m-1} + V[m]^T Y[m] (lower, ascending m; upper is the mirror).  This
 // is a diagonal-transition scan; chunked exactly like matmul_lower.  States are stored ROW-major (j*K + k) as

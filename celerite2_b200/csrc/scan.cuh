@@ -144,15 +144,12 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   const int64_t warps = batch * nblk;
   const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
   if (lv.nlev > 1) {
-    scan_up_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("scan_up_warp", stream, scan_up_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes));
   }
   if (lv.nlev - 1 > kWarpLevels) {
-    scan_top<Mon><<<(unsigned)batch, 256, 0, stream>>>(J, K, lv, nodes, states, init);
-    C2B_CHECK_LAUNCH();
+    C2B_LAUNCH("scan_top", stream, scan_top<Mon><<<(unsigned)batch, 256, 0, stream>>>(J, K, lv, nodes, states, init));
   }
-  scan_down_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes, states, init);
-  C2B_CHECK_LAUNCH();
+  C2B_LAUNCH("scan_down_warp", stream, scan_down_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes, states, init));
   return C2B_OK;
 }
 

@@ -253,3 +253,12 @@ def norm_logdet(d, z, want_grad=False):
         _scratch[key] = buf
     check(lib.c2b_norm_logdet(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(bz), _ptr(bd), buf.data_ptr(), buf.numel(), _stream()))
     return out, bz, bd
+
+
+def add_inplace(x, y):
+    """y += x on the current stream (sum of two cotangents of the same array)."""
+    x, y = _f64(x, "x"), _f64(y, "y")
+    if x.numel() != y.numel():
+        raise ValueError("size mismatch")
+    check(lib.c2b_add_inplace(x.numel(), _ptr(x), _ptr(y), _stream()))
+    return y

@@ -65,6 +65,14 @@ const char *c2b_last_error(void);
 int32_t c2b_device_count(void);
 /* Bytes of scratch the given operation needs for these sizes (M only matters for GENERAL_MATMUL). */
 size_t c2b_scratch_bytes(int32_t op, int64_t N, int64_t M, int32_t J, int32_t K, int64_t batch);
+/*
+ * Built-in kernel timing for benchmarks.  While enabled, every kernel the library launches is bracketed by a
+ * pair of CUDA events on its stream.  c2b_profile_report() waits for the recorded events and returns one line
+ * per (entry point, kernel): "<entry>/<kernel> <launches> <total ms>".  Enabling (or disabling) clears the
+ * record.  The returned string stays valid until the next call.
+ */
+void c2b_profile_enable(int32_t on);
+const char *c2b_profile_report(void);
 /* Override the chunk planner (testing / tuning): chunks per series; 0 restores the heuristic. */
 void c2b_set_chunks_per_series(int64_t chunks);
 
@@ -183,6 +191,12 @@ int c2b_general_matmul_upper(int64_t N, int64_t M, int32_t J, int32_t K, const d
  */
 int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd,
                     void *scratch, size_t scratch_bytes, void *stream);
+
+/*
+ * y[i] += x[i], i < n.  The sum of two cotangents of the same array (e.g. the bU of solve_lower_rev and of
+ * factor_rev), which the reference leaves to the autodiff framework (python/celerite2/jax/ops.py:140-151).
+ */
+int c2b_add_inplace(int64_t n, const double *x, double *y, void *stream);
 
 #ifdef __cplusplus
 }
