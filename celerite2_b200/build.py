@@ -22,7 +22,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 WIDTHS_SWEEP = [0, 2, 4, 6, 16]
 WIDTHS_FACTOR = [0, 2, 4, 6]
 UNITS = (
-    [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_pipeline.cu", None)]
+    [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_pipeline.cu", None), ("api_noalloc.cu", None)]
     + [("inst_sweep.cu", w) for w in WIDTHS_SWEEP]
     + [("inst_factor.cu", w) for w in WIDTHS_FACTOR]
 )

@@ -193,6 +193,34 @@ int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, 
                     void *scratch, size_t scratch_bytes, void *stream);
 
 /*
+ * solve_lower for callers that cannot allocate device memory.  (No counterpart in the reference.)
+ *
+ * Some hosts of this library own a fixed set of device buffers and cannot get more while a call is in
+ * flight: an XLA/JAX custom-call handler only sees the buffers the compiler planned for it, a service that
+ * gave the whole GPU to its own memory pool has nothing left to give, and a callback running in the middle of
+ * someone else's step cannot risk the device-wide synchronisation an allocation or a free may trigger.  They
+ * can neither pass the scan scratch c2b_solve_lower wants nor let it call cudaMallocAsync.  This variant
+ * computes exactly what c2b_solve_lower computes, with the scratch in an array built into the library.
+ *
+ *   - limit: c2b_noalloc_scratch_limit() bytes (8 MiB).  Calls whose c2b_scratch_bytes(C2B_OP_SOLVE_LOWER, ...)
+ *     exceeds it fail with C2B_ERR_SCRATCH_TOO_SMALL and an explanatory c2b_last_error(); 8 MiB covers one series
+ *     of N = 1,000,000 at J = 6, K = 1.  The array occupies that much memory on every GPU that loads the library,
+ *     until the process exits.
+ *   - the call itself performs no cudaMalloc / cudaFree / cudaMallocAsync and calls no allocating library
+ *     routine (with c2b_profile_enable off).  Inputs and outputs are still the caller's buffers.
+ *   - first call on a device: looks up the device address of the built-in array (cudaGetSymbolAddress, with
+ *     the calling thread's current device, which must be the device of `stream`) and caches it.  Make this
+ *     first call before starting any stream capture on that device.
+ *   - every call on a device shares the one array, and it keeps the previous call's contents.  Nothing in it
+ *     needs to start at zero (each word is written before it is read within a call), so nothing is cleared.
+ *     Calls that overlap on the GPU -- two streams, two host threads -- race on the array: keep calls to this
+ *     entry point on one stream or order them yourself.
+ */
+size_t c2b_noalloc_scratch_limit(void);
+int c2b_solve_lower_noalloc(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                            const double *W, const double *Y, double *Z, double *F, int32_t flags, void *stream);
+
+/*
  * y[i] += x[i], i < n.  The sum of two cotangents of the same array (e.g. the bU of solve_lower_rev and of
  * factor_rev), which the reference leaves to the autodiff framework (python/celerite2/jax/ops.py:140-151).
  */
