@@ -80,7 +80,12 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols) {
   if (ov > 0) {
     C = ov;
   } else {
-    const int64_t target = 8192;
+    static int64_t target = 0;
+    if (target == 0) {
+      const char *s = getenv("C2B_TARGET_UNITS");
+      target        = s ? atoll(s) : 8192;
+      if (target < 1) target = 8192;
+    }
     const int64_t have   = batch * (cols > 0 ? cols : 1);
     C                    = have >= target ? 1 : (target + have - 1) / have;
     const int64_t maxC   = N / 64;

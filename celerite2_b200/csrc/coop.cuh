@@ -1,0 +1,258 @@
+// Warp-cooperative versions of the summary algebras (monoids.cuh): one warp works on one combine / apply at a
+// time, matrices staged in shared memory, lanes own output elements.  Used for compile-time widths (JT > 0);
+// the thread-serial routines in monoids.cuh remain the run-time-width fallback.
+//
+// Why: the thread-serial J x J combines keep ~10 matrices per thread in local memory; with 32 lanes that is
+// far more than L1 holds, so every access pays L2 latency (r01 profile: 216k cycles per tree level).  Here a
+// combine is a handful of shared-memory phases (~1k cycles).
+#pragma once
+#include "monoids.cuh"
+
+namespace c2b {
+
+// out[i*ldo + j] = (Cadd ? Cadd[i*ldc + j] : 0) + sum_k opA(i,k) * opB(k,j),  i < n, j < m, k < kk
+// opA(i,k) = TA ? A[k*lda + i] : A[i*lda + k];  opB(k,j) = TB ? B[j*ldb + k] : B[k*ldb + j]
+template <bool TA, bool TB>
+C2B_DEV void wmm(int lane, int n, int m, int kk, const double *A, int lda, const double *B, int ldb, const double *Cadd, int ldc,
+                 double *out, int ldo) {
+  for (int e = lane; e < n * m; e += 32) {
+    const int i = e / m, j = e - i * m;
+    double s    = Cadd ? Cadd[i * ldc + j] : 0.0;
+    for (int k = 0; k < kk; ++k) {
+      const double a = TA ? A[k * lda + i] : A[i * lda + k];
+      const double b = TB ? B[j * ldb + k] : B[k * ldb + j];
+      s              = fma(a, b, s);
+    }
+    out[i * ldo + j] = s;
+  }
+}
+
+C2B_DEV void wcopy(int lane, int n, const double *src, double *dst) {
+  for (int e = lane; e < n; e += 32) dst[e] = src[e];
+}
+
+// out = 0.5 (R + R^T) + Cadd   (J x J, all row-major with leading dimension J; out may be global memory)
+C2B_DEV void wsym_add(int lane, int J, const double *R, const double *Cadd, double *out) {
+  for (int e = lane; e < J * J; e += 32) {
+    const int i = e / J, j = e - i * J;
+    out[e]      = 0.5 * (R[i * J + j] + R[j * J + i]) + Cadd[e];
+  }
+}
+
+// Solve Mx X = R in place for the NR columns of R (row-major J x NR in shared memory): lane c < NR takes
+// column c, keeps a private copy of Mx and eliminates with partial pivoting (ge_solve, monoids.cuh).
+template <int JT>
+C2B_DEV void wsolve(int lane, int J, int NR, const double *Mx, double *R) {
+  constexpr int MJ = Width<JT>::MAXJ;
+  if (lane < NR) {
+    double m[MJ * MJ], r[MJ];
+    C2B_UNROLL_J
+    for (int i = 0; i < J; ++i) {
+      C2B_UNROLL_J
+      for (int j = 0; j < J; ++j) m[i * J + j] = Mx[i * J + j];
+      r[i] = R[i * NR + lane];
+    }
+    C2B_UNROLL_J
+    for (int k = 0; k < J; ++k) {
+      int piv     = k;
+      double best = fabs(m[k * J + k]);
+      C2B_UNROLL_J
+      for (int i = 0; i < J; ++i) {
+        if (i > k) {
+          const double v = fabs(m[i * J + k]);
+          if (v > best) {
+            best = v;
+            piv  = i;
+          }
+        }
+      }
+      C2B_UNROLL_J
+      for (int i = 0; i < J; ++i) {
+        if (i > k && i == piv) {
+          C2B_UNROLL_J
+          for (int j = 0; j < J; ++j) {
+            const double tmp = m[k * J + j];
+            m[k * J + j]     = m[i * J + j];
+            m[i * J + j]     = tmp;
+          }
+          const double tmp = r[k];
+          r[k]             = r[i];
+          r[i]             = tmp;
+        }
+      }
+      const double inv = 1.0 / m[k * J + k];
+      C2B_UNROLL_J
+      for (int j = 0; j < J; ++j) m[k * J + j] *= inv;
+      r[k] *= inv;
+      C2B_UNROLL_J
+      for (int i = 0; i < J; ++i) {
+        if (i != k) {
+          const double f = m[i * J + k];
+          C2B_UNROLL_J
+          for (int j = 0; j < J; ++j) m[i * J + j] = fma(-f, m[k * J + j], m[i * J + j]);
+          r[i] = fma(-f, r[k], r[i]);
+        }
+      }
+    }
+    C2B_UNROLL_J
+    for (int i = 0; i < J; ++i) R[i * NR + lane] = r[i];
+  }
+}
+
+template <class Mon>
+struct Coop;  // wsmem(J,K) doubles per warp; wcombine / wapply mirror Mon::combine / Mon::apply
+
+template <int JT>
+struct Coop<AffV<JT>> {
+  __host__ __device__ static int wsmem(int J, int) { return 2 * J * J; }
+  C2B_DEV static void wcombine(int lane, int J, int K, const double *e1, const double *e2, double *out, double *sm) {
+    const int JJ = J * J;
+    double *M1 = sm, *M2 = sm + JJ;
+    wcopy(lane, JJ, e1, M1);
+    wcopy(lane, JJ, e2, M2);
+    __syncwarp();
+    wmm<false, false>(lane, J, J, J, M2, J, M1, J, nullptr, 0, out, J);
+    // b = M2 b1 + b2 : b is J x K with element (j,k) at [j + J*k]
+    const double *b1 = e1 + JJ, *b2 = e2 + JJ;
+    double *b = out + JJ;
+    for (int e = lane; e < J * K; e += 32) {
+      const int k = e / J, i = e - k * J;
+      double s    = b2[e];
+      for (int j = 0; j < J; ++j) s = fma(M2[i * J + j], b1[j + J * k], s);
+      b[e] = s;
+    }
+    __syncwarp();
+  }
+  C2B_DEV static void wapply(int lane, int J, int K, const double *e, const double *sin, double *sout, double *sm) {
+    const int JJ = J * J;
+    double *M = sm;
+    wcopy(lane, JJ, e, M);
+    __syncwarp();
+    const double *b = e + JJ;
+    for (int x = lane; x < J * K; x += 32) {
+      const int k = x / J, i = x - k * J;
+      double s    = b[x];
+      for (int j = 0; j < J; ++j) s = fma(M[i * J + j], sin[j + J * k], s);
+      sout[x] = s;
+    }
+    __syncwarp();
+  }
+};
+
+template <int JT>
+struct Coop<DiagV<JT>> {
+  __host__ __device__ static int wsmem(int, int) { return 0; }
+  C2B_DEV static void wcombine(int lane, int J, int K, const double *e1, const double *e2, double *out, double *) {
+    for (int j = lane; j < J; j += 32) out[j] = e2[j] * e1[j];
+    for (int x = lane; x < J * K; x += 32) {
+      const int j = x % J;
+      out[J + x]  = fma(e2[j], e1[J + x], e2[J + x]);
+    }
+    __syncwarp();
+  }
+  C2B_DEV static void wapply(int lane, int J, int K, const double *e, const double *sin, double *sout, double *) {
+    for (int x = lane; x < J * K; x += 32) {
+      const int j = x % J;
+      sout[x]     = fma(e[j], sin[x], e[J + x]);
+    }
+    __syncwarp();
+  }
+};
+
+template <int JT>
+struct Coop<Cong<JT>> {
+  __host__ __device__ static int wsmem(int J, int) { return 5 * J * J; }
+  C2B_DEV static void wcombine(int lane, int J, int, const double *e1, const double *e2, double *out, double *sm) {
+    const int JJ = J * J;
+    double *M1 = sm, *M2 = sm + JJ, *B1 = sm + 2 * JJ, *T = sm + 3 * JJ, *R = sm + 4 * JJ;
+    wcopy(lane, JJ, e1, M1);
+    wcopy(lane, JJ, e2, M2);
+    wcopy(lane, JJ, e1 + JJ, B1);
+    __syncwarp();
+    wmm<false, false>(lane, J, J, J, M1, J, M2, J, nullptr, 0, out, J);  // M = M1 M2
+    wmm<false, false>(lane, J, J, J, B1, J, M2, J, nullptr, 0, T, J);    // T = B1 M2
+    __syncwarp();
+    wmm<true, false>(lane, J, J, J, M2, J, T, J, nullptr, 0, R, J);  // R = M2^T T
+    __syncwarp();
+    wsym_add(lane, J, R, e2 + JJ, out + JJ);
+    __syncwarp();
+  }
+  C2B_DEV static void wapply(int lane, int J, int, const double *e, const double *sin, double *sout, double *sm) {
+    const int JJ = J * J;
+    double *M = sm, *G = sm + JJ, *T = sm + 2 * JJ, *R = sm + 3 * JJ;
+    wcopy(lane, JJ, e, M);
+    wcopy(lane, JJ, sin, G);
+    __syncwarp();
+    wmm<false, false>(lane, J, J, J, G, J, M, J, nullptr, 0, T, J);
+    __syncwarp();
+    wmm<true, false>(lane, J, J, J, M, J, T, J, nullptr, 0, R, J);
+    __syncwarp();
+    wsym_add(lane, J, R, e + JJ, sout);
+    __syncwarp();
+  }
+};
+
+template <int JT>
+struct Coop<Lft<JT>> {
+  __host__ __device__ static int wsmem(int J, int) { return 13 * J * J; }
+  C2B_DEV static void wcombine(int lane, int J, int, const double *e1, const double *e2, double *out, double *sm) {
+    const int JJ = J * J;
+    double *A1 = sm, *C1 = sm + JJ, *A2 = sm + 2 * JJ, *Q2 = sm + 3 * JJ, *MX = sm + 4 * JJ;
+    double *R = sm + 5 * JJ;  // J x 2J : [A1 | C1] -> [X1 | X2]
+    double *T2 = sm + 7 * JJ, *T3 = sm + 8 * JJ, *RC = sm + 9 * JJ, *RQ = sm + 10 * JJ;
+    wcopy(lane, JJ, e1, A1);
+    wcopy(lane, JJ, e1 + JJ, C1);
+    wcopy(lane, JJ, e2, A2);
+    wcopy(lane, JJ, e2 + 2 * JJ, Q2);
+    __syncwarp();
+    // MX = I + C1 Q2 ; R = [A1 | C1]
+    for (int e = lane; e < JJ; e += 32) {
+      const int i = e / J, j = e - i * J;
+      double s    = (i == j) ? 1.0 : 0.0;
+      for (int k = 0; k < J; ++k) s = fma(C1[i * J + k], Q2[k * J + j], s);
+      MX[e]            = s;
+      R[i * 2 * J + j]     = A1[e];
+      R[i * 2 * J + J + j] = C1[e];
+    }
+    __syncwarp();
+    wsolve<JT>(lane, J, 2 * J, MX, R);
+    __syncwarp();
+    const double *X1 = R, *X2 = R + J;  // leading dimension 2J
+    wmm<false, false>(lane, J, J, J, A2, J, X1, 2 * J, nullptr, 0, out, J);  // A = A2 X1
+    wmm<false, false>(lane, J, J, J, A2, J, X2, 2 * J, nullptr, 0, T2, J);   // T2 = A2 X2
+    wmm<false, false>(lane, J, J, J, Q2, J, X1, 2 * J, nullptr, 0, T3, J);   // T3 = Q2 X1
+    __syncwarp();
+    wmm<false, true>(lane, J, J, J, T2, J, A2, J, nullptr, 0, RC, J);  // RC = T2 A2^T
+    wmm<true, false>(lane, J, J, J, A1, J, T3, J, nullptr, 0, RQ, J);  // RQ = A1^T T3
+    __syncwarp();
+    wsym_add(lane, J, RC, e2 + JJ, out + JJ);
+    wsym_add(lane, J, RQ, e1 + 2 * JJ, out + 2 * JJ);
+    __syncwarp();
+  }
+  C2B_DEV static void wapply(int lane, int J, int, const double *e, const double *sin, double *sout, double *sm) {
+    const int JJ = J * J;
+    double *A = sm, *Q = sm + JJ, *X = sm + 2 * JJ, *MX = sm + 3 * JJ, *Z = sm + 4 * JJ, *T = sm + 5 * JJ, *R = sm + 6 * JJ;
+    wcopy(lane, JJ, e, A);
+    wcopy(lane, JJ, e + 2 * JJ, Q);
+    wcopy(lane, JJ, sin, X);
+    __syncwarp();
+    for (int x = lane; x < JJ; x += 32) {
+      const int i = x / J, j = x - i * J;
+      double s    = (i == j) ? 1.0 : 0.0;
+      for (int k = 0; k < J; ++k) s = fma(X[i * J + k], Q[k * J + j], s);
+      MX[x] = s;
+      Z[x]  = X[x];
+    }
+    __syncwarp();
+    wsolve<JT>(lane, J, J, MX, Z);  // Z = (I + X Q)^-1 X
+    __syncwarp();
+    wmm<false, false>(lane, J, J, J, A, J, Z, J, nullptr, 0, T, J);
+    __syncwarp();
+    wmm<false, true>(lane, J, J, J, T, J, A, J, nullptr, 0, R, J);
+    __syncwarp();
+    wsym_add(lane, J, R, e + JJ, sout);
+    __syncwarp();
+  }
+};
+
+}  // namespace c2b

@@ -124,6 +124,8 @@ C2B_PRAGMA(unroll NRU)
 // element: M (J*J, row-major) then b (J*K, index j + J*k).  state: G (J*K, index j + J*k).
 template <int JT>
 struct AffV {
+  static constexpr bool kCoop = JT > 0;  // warp-cooperative scan (coop.cuh) for compile-time widths
+  static constexpr int kJT    = JT;
   static constexpr int MJ = Width<JT>::MAXJ;
   __host__ __device__ static int esize(int J, int K) { return J * J + J * K; }
   __host__ __device__ static int ssize(int J, int K) { return J * K; }
@@ -173,6 +175,8 @@ struct AffV {
 // element: m (J) then b (J*K).  state: G (J*K).
 template <int JT>
 struct DiagV {
+  static constexpr bool kCoop = JT > 0;  // warp-cooperative scan (coop.cuh) for compile-time widths
+  static constexpr int kJT    = JT;
   __host__ __device__ static int esize(int J, int K) { return J + J * K; }
   __host__ __device__ static int ssize(int J, int K) { return J * K; }
   C2B_DEV static void combine(int J, int K, const double *e1, const double *e2, double *out) {
@@ -191,6 +195,8 @@ struct DiagV {
 // apply: M^T G M + B.   combine(first, second): (M1 M2, M2^T B1 M2 + B2).
 template <int JT>
 struct Cong {
+  static constexpr bool kCoop = JT > 0;  // warp-cooperative scan (coop.cuh) for compile-time widths
+  static constexpr int kJT    = JT;
   static constexpr int MJ = Width<JT>::MAXJ;
   __host__ __device__ static int esize(int J, int) { return 2 * J * J; }
   __host__ __device__ static int ssize(int J, int) { return J * J; }
@@ -244,6 +250,8 @@ struct Cong {
 // combine: Minv = (I + C1 Q2)^-1;  A = A2 Minv A1;  C = A2 Minv C1 A2^T + C2;  Q = A1^T Q2 Minv A1 + Q1
 template <int JT>
 struct Lft {
+  static constexpr bool kCoop = JT > 0;  // warp-cooperative scan (coop.cuh) for compile-time widths
+  static constexpr int kJT    = JT;
   static constexpr int MJ = Width<JT>::MAXJ;
   __host__ __device__ static int esize(int J, int) { return 3 * J * J; }
   __host__ __device__ static int ssize(int J, int) { return J * J; }

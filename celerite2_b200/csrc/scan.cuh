@@ -8,7 +8,7 @@
 // above by one CTA per series, the way back down mirrors that.  The state entering the first chunk is zero or
 // a caller-supplied carry (the hand-off point for sharding one series across GPUs).
 #pragma once
-#include "monoids.cuh"
+#include "coop.cuh"
 
 namespace c2b {
 
@@ -61,7 +61,8 @@ C2B_DEV void down_node(int J, int K, const Levels &lv, const double *nodes, doub
 
 // one warp per (series, block of 32 leaves): levels 1..min(5, top)
 template <class Mon>
-__global__ void scan_up_warp(int J, int K, int64_t batch, Levels lv, double *nodes_all) {
+__global__ void scan_up_warp(int J_, int K, int64_t batch, Levels lv, double *nodes_all) {
+  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
   const int64_t nblk = (lv.count[0] + 31) / 32;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane     = threadIdx.x & 31;
@@ -79,7 +80,8 @@ __global__ void scan_up_warp(int J, int K, int64_t batch, Levels lv, double *nod
 
 // one CTA per series: levels 6..top up, then top..6 down (leaves states at level 5)
 template <class Mon>
-__global__ void scan_top(int J, int K, Levels lv, double *nodes_all, double *states_all, const double *init) {
+__global__ void scan_top(int J_, int K, Levels lv, double *nodes_all, double *states_all, const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
   const int64_t b = blockIdx.x;
   const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
   double *nodes  = nodes_all + b * lv.total * es;
@@ -102,7 +104,8 @@ __global__ void scan_top(int J, int K, Levels lv, double *nodes_all, double *sta
 
 // one warp per (series, block of 32 leaves): levels min(5, top)..1 down
 template <class Mon>
-__global__ void scan_down_warp(int J, int K, int64_t batch, Levels lv, const double *nodes_all, double *states_all, const double *init) {
+__global__ void scan_down_warp(int J_, int K, int64_t batch, Levels lv, const double *nodes_all, double *states_all, const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
   const int64_t nblk = (lv.count[0] + 31) / 32;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane     = threadIdx.x & 31;
@@ -126,6 +129,109 @@ __global__ void scan_down_warp(int J, int K, int64_t batch, Levels lv, const dou
   }
 }
 
+// ---- warp-cooperative variants (compile-time widths) -------------------------------------------------------------
+template <class Mon>
+C2B_DEV void wup_node(int lane, int J, int K, const Levels &lv, double *nodes, int es, int l, int64_t idx, double *sm) {
+  const double *left = nodes + (lv.off[l - 1] + 2 * idx) * es;
+  double *out        = nodes + (lv.off[l] + idx) * es;
+  if (2 * idx + 1 < lv.count[l - 1]) {
+    Coop<Mon>::wcombine(lane, J, K, left, left + es, out, sm);
+  } else {
+    wcopy(lane, es, left, out);
+    __syncwarp();
+  }
+}
+
+template <class Mon>
+C2B_DEV void wdown_node(int lane, int J, int K, const Levels &lv, const double *nodes, double *states, int es, int ss, int l,
+                        int64_t idx, double *sm) {
+  const double *sin = states + (lv.off[l] + idx) * ss;
+  double *s0        = states + (lv.off[l - 1] + 2 * idx) * ss;
+  wcopy(lane, ss, sin, s0);
+  if (2 * idx + 1 < lv.count[l - 1]) Coop<Mon>::wapply(lane, J, K, nodes + (lv.off[l - 1] + 2 * idx) * es, sin, s0 + ss, sm);
+  __syncwarp();
+}
+
+constexpr int kCoopLeaves = 32;  // leaves per warp block
+constexpr int kCoopLevels = 5;
+
+template <class Mon>
+__global__ void scan_up_coop(int J_, int K, int64_t batch, Levels lv, double *nodes_all) {
+  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
+  extern __shared__ double sm_all[];
+  const int wsm      = Coop<Mon>::wsmem(J, K);
+  const int wib      = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *sm         = sm_all + (size_t)wib * wsm;
+  const int64_t nblk = (lv.count[0] + kCoopLeaves - 1) / kCoopLeaves;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+  if (warp >= batch * nblk) return;
+  const int64_t b = warp / nblk, blk = warp % nblk;
+  const int es  = Mon::esize(J, K);
+  double *nodes = nodes_all + b * lv.total * es;
+  const int top = lv.nlev - 1 < kCoopLevels ? lv.nlev - 1 : kCoopLevels;
+  for (int l = 1; l <= top; ++l) {
+    const int64_t first = (blk * kCoopLeaves) >> l;
+    for (int r = 0; r < (kCoopLeaves >> l); ++r)
+      if (first + r < lv.count[l]) wup_node<Mon>(lane, J, K, lv, nodes, es, l, first + r, sm);
+    __syncwarp();
+  }
+}
+
+template <class Mon>
+__global__ void __launch_bounds__(512) scan_top_coop(int J_, int K, Levels lv, double *nodes_all, double *states_all, const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
+  extern __shared__ double sm_all[];
+  const int wsm  = Coop<Mon>::wsmem(J, K);
+  const int wib  = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  double *sm     = sm_all + (size_t)wib * wsm;
+  const int64_t b = blockIdx.x;
+  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
+  double *nodes  = nodes_all + b * lv.total * es;
+  double *states = states_all + b * lv.total * ss;
+  const int top  = lv.nlev - 1;
+  for (int l = kCoopLevels + 1; l <= top; ++l) {
+    for (int64_t idx = wib; idx < lv.count[l]; idx += nw) wup_node<Mon>(lane, J, K, lv, nodes, es, l, idx, sm);
+    __syncthreads();
+  }
+  {
+    double *st = states + lv.off[top] * ss;
+    for (int i = threadIdx.x; i < ss; i += blockDim.x) st[i] = init ? init[b * ss + i] : 0.0;
+  }
+  __syncthreads();
+  for (int l = top; l > kCoopLevels; --l) {
+    for (int64_t idx = wib; idx < lv.count[l]; idx += nw) wdown_node<Mon>(lane, J, K, lv, nodes, states, es, ss, l, idx, sm);
+    __syncthreads();
+  }
+}
+
+template <class Mon>
+__global__ void scan_down_coop(int J_, int K, int64_t batch, Levels lv, const double *nodes_all, double *states_all, const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
+  extern __shared__ double sm_all[];
+  const int wsm      = Coop<Mon>::wsmem(J, K);
+  const int wib      = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double *sm         = sm_all + (size_t)wib * wsm;
+  const int64_t nblk = (lv.count[0] + kCoopLeaves - 1) / kCoopLeaves;
+  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+  if (warp >= batch * nblk) return;
+  const int64_t b = warp / nblk, blk = warp % nblk;
+  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
+  const double *nodes = nodes_all + b * lv.total * es;
+  double *states      = states_all + b * lv.total * ss;
+  const int top       = lv.nlev - 1 < kCoopLevels ? lv.nlev - 1 : kCoopLevels;
+  if (lv.nlev - 1 <= kCoopLevels) {
+    double *st = states + lv.off[top] * ss;
+    for (int i = lane; i < ss; i += 32) st[i] = init ? init[b * ss + i] : 0.0;
+    __syncwarp();
+  }
+  for (int l = top; l >= 1; --l) {
+    const int64_t first = (blk * kCoopLeaves) >> l;
+    for (int r = 0; r < (kCoopLeaves >> l); ++r)
+      if (first + r < lv.count[l]) wdown_node<Mon>(lane, J, K, lv, nodes, states, es, ss, l, first + r, sm);
+    __syncwarp();
+  }
+}
+
 // Scratch needed by a scan over `leaves` chunks per series.
 template <class Mon>
 static inline void scan_sizes(int J, int K, int64_t batch, int64_t leaves, size_t *node_doubles, size_t *state_doubles) {
@@ -140,6 +246,21 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
                            cudaStream_t stream) {
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
+  if constexpr (Mon::kCoop) {
+    const int wsm       = Coop<Mon>::wsmem(J, K);
+    const size_t smem1  = (size_t)wsm * sizeof(double);  // one warp per CTA: spreads the blocks over all SMs
+    const unsigned grid = (unsigned)(batch * nblk);
+    if (lv.nlev > 1) C2B_LAUNCH("scan_up_coop", stream, scan_up_coop<Mon><<<grid, 32, smem1, stream>>>(J, K, batch, lv, nodes));
+    if (lv.nlev - 1 > kCoopLevels) {
+      const int nw = 16;  // 512 threads: leaves 128 registers per thread for the private elimination
+      if ((size_t)nw * smem1 > 48 * 1024)
+        C2B_CUDA(cudaFuncSetAttribute(scan_top_coop<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)nw * smem1)));
+      C2B_LAUNCH("scan_top_coop", stream,
+                 scan_top_coop<Mon><<<(unsigned)batch, nw * 32, (size_t)nw * smem1, stream>>>(J, K, lv, nodes, states, init));
+    }
+    C2B_LAUNCH("scan_down_coop", stream, scan_down_coop<Mon><<<grid, 32, smem1, stream>>>(J, K, batch, lv, nodes, states, init));
+    return C2B_OK;
+  } else {
   const int threads  = 128;  // 4 warps
   const int64_t warps = batch * nblk;
   const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
@@ -151,6 +272,7 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   }
   C2B_LAUNCH("scan_down_warp", stream, scan_down_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes, states, init));
   return C2B_OK;
+  }
 }
 
 // Finalise a reverse op: add the bt term each chunk owes its neighbour and reduce the per-chunk bc partials in
