@@ -30,12 +30,12 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
 
-_COMMON = ["common.cuh", "monoids.cuh", "scan.cuh", "args.cuh", "host_common.cuh"]
+_COMMON = ["common.cuh", "monoids.cuh", "coop.cuh", "scan.cuh", "args.cuh", "host_common.cuh"]
 _EXTRA = {
     "api_misc.cu": ["misc.cuh"],
     "api_pipeline.cu": ["misc.cuh"],
-    "inst_sweep.cu": ["sweep.cuh"],
-    "inst_factor.cu": ["factor.cuh"],
+    "inst_sweep.cu": ["sweep.cuh", "fast_sweep.cuh", "tile.cuh"],
+    "inst_factor.cu": ["factor.cuh", "fast_factor.cuh", "tile.cuh"],
 }
 
 

@@ -95,6 +95,7 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols) {
   if (C < 1) C = 1;
   if (C > 32768) C = 32768;
   pl.L = (N + C - 1) / C;
+  if (C > 1 && (pl.L & 1)) pl.L += 1;  // even chunk starts keep the 8-byte-per-row arrays 16-byte aligned for bulk copies
   pl.C = (N + pl.L - 1) / pl.L;
   return pl;
 }

@@ -135,6 +135,69 @@ C2B_DEV void compute_p(int J, const double *c, const unsigned *dup, double dt, d
   }
 }
 
+// ---- per-thread software pipeline of input rows -----------------------------------------------------------------
+// The recursions walk their chunk row by row with a dependent chain per row, and every row needs a handful of
+// small, thread-private loads (t, a, one row of U, V, ...).  Issued at the point of use they expose the full
+// DRAM latency three or four times per row (r01 profile: >70 % of the stall samples).  RowPipe issues the loads
+// of row i+D with cp.async (LDGSTS, 8 bytes each, no registers held) into a ring of D+1 shared-memory slots
+// while row i is being computed.  Layout [slot][field][thread]: lanes read consecutive words, no bank conflicts.
+// STAGE = false (run-time widths) degenerates to plain loads into a local array at the top of each row.
+C2B_DEV void cp_async8(double *smem_dst, const double *gmem_src) {
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem_src) : "memory");
+}
+C2B_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+C2B_DEV void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <bool STAGE, int ROWD, int NSLOT>
+struct RowPipe {
+  static constexpr int D = STAGE ? NSLOT - 1 : 0;  // rows of look-ahead
+  double *base;                                     // shared memory (STAGE)
+  double row[STAGE ? 1 : ROWD];                     // direct mode: the current row
+  int nt, tid, slot_put, slot_get;
+  C2B_DEV void init(double *smem) {
+    base     = smem;
+    nt       = blockDim.x;
+    tid      = threadIdx.x;
+    slot_put = 0;
+    slot_get = 0;
+  }
+  // store field f of the row being fetched
+  C2B_DEV void put(int f, const double *g) {
+    if (STAGE)
+      cp_async8(base + ((size_t)(slot_put * ROWD + f) * nt + tid), g);
+    else
+      row[f] = *g;
+  }
+  C2B_DEV void put_value(int f, double v) {
+    if (STAGE)
+      base[(size_t)(slot_put * ROWD + f) * nt + tid] = v;
+    else
+      row[f] = v;
+  }
+  // end of one row's fetch (called once per loop trip even when nothing was fetched, to keep group counts uniform)
+  C2B_DEV void commit(bool fetched) {
+    if (STAGE) {
+      cp_async_commit();
+      if (fetched) slot_put = (slot_put + 1 == NSLOT) ? 0 : slot_put + 1;
+    }
+  }
+  // make the oldest outstanding row readable
+  C2B_DEV void acquire() {
+    if (STAGE) cp_async_wait<D>();
+  }
+  C2B_DEV double get(int f) const {
+    if (STAGE) return base[(size_t)(slot_get * ROWD + f) * nt + tid];
+    return row[f];
+  }
+  C2B_DEV void release() {
+    if (STAGE) slot_get = (slot_get + 1 == NSLOT) ? 0 : slot_get + 1;
+  }
+};
+
 // First failing row of factor(): keep the smallest positive index (0 = success).
 C2B_DEV void record_failure(int64_t *status, int64_t n) {
   if (!status) return;

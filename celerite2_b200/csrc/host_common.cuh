@@ -31,6 +31,24 @@ static inline void launch_shape(int64_t units, unsigned *grid, unsigned *block) 
   if (*grid == 0) *grid = 1;
 }
 
+// Staged kernels (compile-time widths) keep a per-thread ring of input rows in dynamic shared memory:
+// slots * row_doubles * 8 bytes per thread.  One warp per CTA keeps the footprint small and lets many CTAs share an SM.
+template <typename Kernel>
+static inline int staged_shape(Kernel kernel, int64_t units, bool staged, int slots, int row_doubles, unsigned *grid, unsigned *block,
+                               size_t *smem) {
+  if (!staged) {
+    launch_shape(units, grid, block);
+    *smem = 0;
+    return C2B_OK;
+  }
+  *block = 32;
+  *grid  = (unsigned)((units + 31) / 32);
+  if (*grid == 0) *grid = 1;
+  *smem = (size_t)slots * row_doubles * 32 * sizeof(double);
+  if (*smem > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
+  return C2B_OK;
+}
+
 static inline int check_common(int64_t N, int J, int64_t batch) {
   if (N < 1) {
     set_error("N must be >= 1 (got %lld)", (long long)N);

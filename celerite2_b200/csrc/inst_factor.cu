@@ -1,6 +1,9 @@
 // Launchers of the factor / factor_rev kernels for ONE compile-time width (C2B_JT); see args.cuh.
+#include <stdlib.h>
+
 #include "host_common.cuh"
 #include "factor.cuh"
+#include "fast_factor.cuh"
 
 #ifndef C2B_JT
 #error "compile with -DC2B_JT=<width> (0 = run-time width)"
@@ -8,36 +11,69 @@
 
 namespace c2b {
 
+// compile-time widths: TMA tile pipeline (fast_factor.cuh)
+template <int JT>
+static int launch_factor_fast(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
+  if constexpr (JT > 0) {
+    using Lay = FFactorLayout<JT>;
+    const unsigned grid = (unsigned)((g.batch * g.C + 31) / 32);
+    if (g.C > 1) {
+      g.leaves      = sb.nodes;
+      g.node_stride = sb.node_stride;
+      const size_t sm1 = TilePipe<kFT, Lay::SIN, Lay::SOUT_SUMMARY>::kSmemBytes;
+      if (sm1 > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(ffactor_summary_kernel<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+      C2B_LAUNCH("ffactor_summary_kernel", stream, ffactor_summary_kernel<JT><<<grid, 32, sm1, stream>>>(g));
+      int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      g.carry = sb.states;
+    }
+    const size_t sm2 = TilePipe<kFT, Lay::SIN, Lay::SOUT>::kSmemBytes;
+    if (sm2 > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(ffactor_apply_kernel<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+    C2B_LAUNCH("ffactor_apply_kernel", stream, ffactor_apply_kernel<JT><<<grid, 32, sm2, stream>>>(g));
+  }
+  return C2B_OK;
+}
+
 template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
+  if (JT > 0 && getenv("C2B_TMA")) return launch_factor_fast<JT>(g, sb, stream);  // experimental, see DESIGN.md
   unsigned grid, block;
-  launch_shape(g.batch * g.C, &grid, &block);
+  size_t smem;
+  int rcs;
   if (g.C > 1) {
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
-    C2B_LAUNCH("factor_summary_kernel", stream, factor_summary_kernel<JT><<<grid, block, 0, stream>>>(g));
+    rcs = staged_shape(factor_summary_kernel<JT>, g.batch * g.C, JT > 0, kFactorSlots, FactorRow<JT>::ROWD, &grid, &block, &smem);
+    if (rcs) return rcs;
+    C2B_LAUNCH("factor_summary_kernel", stream, factor_summary_kernel<JT><<<grid, block, smem, stream>>>(g));
     int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
-  C2B_LAUNCH("factor_apply_kernel", stream, factor_apply_kernel<JT><<<grid, block, 0, stream>>>(g));
+  rcs = staged_shape(factor_apply_kernel<JT>, g.batch * g.C, JT > 0, kFactorSlots, FactorRow<JT>::ROWD, &grid, &block, &smem);
+  if (rcs) return rcs;
+  C2B_LAUNCH("factor_apply_kernel", stream, factor_apply_kernel<JT><<<grid, block, smem, stream>>>(g));
   return C2B_OK;
 }
 
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   unsigned grid, block;
+  size_t smem;
+  int rcs;
   if (g.C > 1) {
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
-    launch_shape(g.batch * g.C * (g.J + 1), &grid, &block);
-    C2B_LAUNCH("factor_rev_summary_kernel", stream, factor_rev_summary_kernel<JT><<<grid, block, 0, stream>>>(g));
+    rcs = staged_shape(factor_rev_summary1_kernel<JT>, g.batch * g.C, JT > 0, kFactorRevSlots, FactorRevRow<JT>::ROWD, &grid, &block, &smem);
+    if (rcs) return rcs;
+    C2B_LAUNCH("factor_rev_summary1_kernel", stream, factor_rev_summary1_kernel<JT><<<grid, block, smem, stream>>>(g));
     int rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
-  launch_shape(g.batch * g.C, &grid, &block);
-  C2B_LAUNCH("factor_rev_apply_kernel", stream, factor_rev_apply_kernel<JT><<<grid, block, 0, stream>>>(g));
+  rcs = staged_shape(factor_rev_apply_kernel<JT>, g.batch * g.C, JT > 0, kFactorRevSlots, FactorRevRow<JT>::ROWD, &grid, &block, &smem);
+  if (rcs) return rcs;
+  C2B_LAUNCH("factor_rev_apply_kernel", stream, factor_rev_apply_kernel<JT><<<grid, block, smem, stream>>>(g));
   C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<(unsigned)g.batch, 256, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc));
   return C2B_OK;
 }

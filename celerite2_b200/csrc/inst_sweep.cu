@@ -11,12 +11,22 @@ namespace c2b {
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   unsigned grid, block;
+  size_t smem;
+  int rcs;
   if (a.C > 1) {
     a.leaves      = sb.nodes;
     a.node_stride = sb.node_stride;
     const int ncol = SOLVE ? a.J + a.K : a.K;
-    launch_shape(a.batch * a.C * ncol, &grid, &block);
-    C2B_LAUNCH("sweep_summary_kernel", stream, sweep_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
+    if (SOLVE && a.K == 1) {
+      rcs = staged_shape(sweep_summary1_kernel<JT, LOWER>, a.batch * a.C, JT > 0, kSweepSlots, SweepRow<JT>::ROWD, &grid, &block, &smem);
+      if (rcs) return rcs;
+      C2B_LAUNCH("sweep_summary1_kernel", stream, sweep_summary1_kernel<JT, LOWER><<<grid, block, smem, stream>>>(a));
+    } else {
+      rcs = staged_shape(sweep_summary_kernel<JT, SOLVE, LOWER>, a.batch * a.C * ncol, JT > 0, kSweepSlots, SweepRow<JT>::ROWD, &grid,
+                         &block, &smem);
+      if (rcs) return rcs;
+      C2B_LAUNCH("sweep_summary_kernel", stream, sweep_summary_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
+    }
     int rc;
     if (SOLVE)
       rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
@@ -25,20 +35,32 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
     if (rc) return rc;
     a.carry = sb.states;
   }
-  launch_shape(a.batch * a.C * a.K, &grid, &block);
-  C2B_LAUNCH("sweep_apply_kernel", stream, sweep_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
+  rcs = staged_shape(sweep_apply_kernel<JT, SOLVE, LOWER>, a.batch * a.C * a.K, JT > 0, kSweepSlots, SweepRow<JT>::ROWD, &grid, &block, &smem);
+  if (rcs) return rcs;
+  C2B_LAUNCH("sweep_apply_kernel", stream, sweep_apply_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
   return C2B_OK;
 }
 
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   unsigned grid, block;
+  size_t smem;
+  int rcs;
   if (a.C > 1) {
     a.leaves      = sb.nodes;
     a.node_stride = sb.node_stride;
     const int ncol = SOLVE ? a.J + a.K : a.K;
-    launch_shape(a.batch * a.C * ncol, &grid, &block);
-    C2B_LAUNCH("sweep_rev_summary_kernel", stream, sweep_rev_summary_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
+    if (SOLVE && a.K == 1) {
+      rcs = staged_shape(sweep_rev_summary1_kernel<JT, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
+                         &smem);
+      if (rcs) return rcs;
+      C2B_LAUNCH("sweep_rev_summary1_kernel", stream, sweep_rev_summary1_kernel<JT, LOWER><<<grid, block, smem, stream>>>(a));
+    } else {
+      rcs = staged_shape(sweep_rev_summary_kernel<JT, SOLVE, LOWER>, a.batch * a.C * ncol, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD,
+                         &grid, &block, &smem);
+      if (rcs) return rcs;
+      C2B_LAUNCH("sweep_rev_summary_kernel", stream, sweep_rev_summary_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
+    }
     int rc;
     if (SOLVE)
       rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
@@ -47,8 +69,10 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
     if (rc) return rc;
     a.carry = sb.states;
   }
-  launch_shape(a.batch * a.C, &grid, &block);
-  C2B_LAUNCH("sweep_rev_apply_kernel", stream, sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, 0, stream>>>(a));
+  rcs = staged_shape(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
+                     &smem);
+  if (rcs) return rcs;
+  C2B_LAUNCH("sweep_rev_apply_kernel", stream, sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
   C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<(unsigned)a.batch, 256, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc));
   return C2B_OK;
 }
