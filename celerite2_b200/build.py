@@ -34,8 +34,8 @@ _COMMON = ["common.cuh", "monoids.cuh", "coop.cuh", "scan.cuh", "args.cuh", "hos
 _EXTRA = {
     "api_misc.cu": ["misc.cuh"],
     "api_pipeline.cu": ["misc.cuh"],
-    "inst_sweep.cu": ["sweep.cuh", "fast_sweep.cuh", "tile.cuh"],
-    "inst_factor.cu": ["factor.cuh", "fast_factor.cuh", "tile.cuh"],
+    "inst_sweep.cu": ["sweep.cuh", "group.cuh", "gsweep.cuh"],
+    "inst_factor.cu": ["factor.cuh", "fast_factor.cuh", "tile.cuh", "group.cuh", "gfactor.cuh"],
 }
 
 

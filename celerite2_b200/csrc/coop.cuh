@@ -39,63 +39,52 @@ C2B_DEV void wsym_add(int lane, int J, const double *R, const double *Cadd, doub
   }
 }
 
-// Solve Mx X = R in place for the NR columns of R (row-major J x NR in shared memory): lane c < NR takes
-// column c, keeps a private copy of Mx and eliminates with partial pivoting (ge_solve, monoids.cuh).
-template <int JT>
-C2B_DEV void wsolve(int lane, int J, int NR, const double *Mx, double *R) {
-  constexpr int MJ = Width<JT>::MAXJ;
-  if (lane < NR) {
-    double m[MJ * MJ], r[MJ];
-    C2B_UNROLL_J
-    for (int i = 0; i < J; ++i) {
-      C2B_UNROLL_J
-      for (int j = 0; j < J; ++j) m[i * J + j] = Mx[i * J + j];
-      r[i] = R[i * NR + lane];
-    }
-    C2B_UNROLL_J
-    for (int k = 0; k < J; ++k) {
-      int piv     = k;
-      double best = fabs(m[k * J + k]);
-      C2B_UNROLL_J
-      for (int i = 0; i < J; ++i) {
-        if (i > k) {
-          const double v = fabs(m[i * J + k]);
-          if (v > best) {
-            best = v;
-            piv  = i;
-          }
-        }
-      }
-      C2B_UNROLL_J
-      for (int i = 0; i < J; ++i) {
-        if (i > k && i == piv) {
-          C2B_UNROLL_J
-          for (int j = 0; j < J; ++j) {
-            const double tmp = m[k * J + j];
-            m[k * J + j]     = m[i * J + j];
-            m[i * J + j]     = tmp;
-          }
-          const double tmp = r[k];
-          r[k]             = r[i];
-          r[i]             = tmp;
-        }
-      }
-      const double inv = 1.0 / m[k * J + k];
-      C2B_UNROLL_J
-      for (int j = 0; j < J; ++j) m[k * J + j] *= inv;
-      r[k] *= inv;
-      C2B_UNROLL_J
-      for (int i = 0; i < J; ++i) {
-        if (i != k) {
-          const double f = m[i * J + k];
-          C2B_UNROLL_J
-          for (int j = 0; j < J; ++j) m[i * J + j] = fma(-f, m[k * J + j], m[i * J + j]);
-          r[i] = fma(-f, r[k], r[i]);
-        }
+// Solve Mx X = R in place (Mx: J x J, R: J x NR, both row-major in shared memory; Mx is destroyed) by Gauss-Jordan
+// elimination with partial pivoting, the whole warp working on one system: per pivot step the lanes find the
+// pivot row (shuffle arg-max), swap, scale the pivot row and eliminate it from all other rows, each lane owning
+// elements of the augmented matrix.  Four short shared-memory phases per step instead of a long private chain.
+C2B_DEV void wsolve(int lane, int J, int NR, double *Mx, double *R) {
+  const int NC = J + NR;  // columns of the augmented matrix [Mx | R]
+  for (int k = 0; k < J; ++k) {
+    // pivot search over rows k..J-1 (J <= 32)
+    double v = (lane >= k && lane < J) ? fabs(Mx[lane * J + k]) : -1.0;
+    int piv  = lane;
+    for (int o = 16; o > 0; o >>= 1) {
+      const double v2 = __shfl_xor_sync(0xffffffffu, v, o);
+      const int p2    = __shfl_xor_sync(0xffffffffu, piv, o);
+      if (v2 > v || (v2 == v && p2 < piv)) {
+        v   = v2;
+        piv = p2;
       }
     }
-    C2B_UNROLL_J
-    for (int i = 0; i < J; ++i) R[i * NR + lane] = r[i];
+    // swap rows k and piv, scale the pivot row
+    const double inv = 1.0 / Mx[piv * J + k];
+    __syncwarp();
+    for (int cidx = lane; cidx < NC; cidx += 32) {
+      double *col       = cidx < J ? Mx + cidx : R + (cidx - J);
+      const int ld      = cidx < J ? J : NR;
+      const double top  = col[k * ld];
+      const double pivv = col[piv * ld];
+      col[piv * ld]     = top;
+      col[k * ld]       = pivv * inv;
+    }
+    __syncwarp();
+    // eliminate column k from every other row (columns > k of Mx and all of R)
+    const int ncols = (J - k - 1) + NR;
+    for (int e = lane; e < (J - 1) * ncols; e += 32) {
+      int i       = e / ncols;
+      const int q = e - i * ncols;
+      if (i >= k) ++i;  // skip the pivot row
+      const double f = Mx[i * J + k];
+      if (q < J - k - 1) {
+        const int cidx = k + 1 + q;
+        Mx[i * J + cidx] = fma(-f, Mx[k * J + cidx], Mx[i * J + cidx]);
+      } else {
+        const int cidx = q - (J - k - 1);
+        R[i * NR + cidx] = fma(-f, R[k * NR + cidx], R[i * NR + cidx]);
+      }
+    }
+    __syncwarp();
   }
 }
 
@@ -215,7 +204,7 @@ struct Coop<Lft<JT>> {
       R[i * 2 * J + J + j] = C1[e];
     }
     __syncwarp();
-    wsolve<JT>(lane, J, 2 * J, MX, R);
+    wsolve(lane, J, 2 * J, MX, R);
     __syncwarp();
     const double *X1 = R, *X2 = R + J;  // leading dimension 2J
     wmm<false, false>(lane, J, J, J, A2, J, X1, 2 * J, nullptr, 0, out, J);  // A = A2 X1
@@ -244,7 +233,7 @@ struct Coop<Lft<JT>> {
       Z[x]  = X[x];
     }
     __syncwarp();
-    wsolve<JT>(lane, J, J, MX, Z);  // Z = (I + X Q)^-1 X
+    wsolve(lane, J, J, MX, Z);  // Z = (I + X Q)^-1 X
     __syncwarp();
     wmm<false, false>(lane, J, J, J, A, J, Z, J, nullptr, 0, T, J);
     __syncwarp();

@@ -1,0 +1,282 @@
+// Lane-group kernels of the K == 1 sweeps (solve / matmul, lower / upper) and of their reverse mode.
+// apply: lane c of a group holds element c of the J-vector state; summary of the solves: lane q holds the whole
+// J-vector of column q (q < J: unit vectors -> transition M, q == J: the real right-hand side -> b).
+#pragma once
+#include "group.cuh"
+#include "sweep.cuh"
+
+namespace c2b {
+
+constexpr int kGroupThreadsS = 128;
+
+// ---- forward apply -----------------------------------------------------------------------------------------------
+template <int J, bool SOLVE, bool LOWER>
+__global__ void __launch_bounds__(kGroupThreadsS) gsweep_apply_kernel(SweepArgs a) {
+  constexpr int G  = GroupOf<J>::G;
+  constexpr int GP = kGroupThreadsS / G;
+  const int c         = threadIdx.x & (G - 1);
+  const int64_t unit  = (int64_t)blockIdx.x * GP + threadIdx.x / G;
+  const bool has      = unit < a.batch * a.C;
+  const bool act      = has && c < J;
+  const int64_t chunk = has ? unit % a.C : 0, b = has ? unit / a.C : 0;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
+  const double *t     = a.t + b * a.t_bs;
+  const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
+  double *Z = a.Z + b * a.N, *F = a.F ? a.F + b * a.N * J : nullptr;
+  const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
+  double Fc = 0.0;
+  if (a.carry && act) {
+    const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
+    Fc                 = a.carry[(b * a.node_stride + leaf) * (int64_t)J + c];
+  }
+  const int cnt   = (int)(n1 - n0);
+  const int trips = warp_max(cnt);
+  auto row = [&](int i) { return LOWER ? n0 + i : n1 - 1 - i; };
+  double tn = 0.0, to = 0.0, an = 0.0, bn = 0.0, yn = 0.0, zn = 0.0;
+  auto load = [&](int i) {
+    const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
+    tn = t[n];
+    to = (o >= 0 && o < a.N) ? t[o] : tn;
+    yn = Y[n];
+    if (!SOLVE) zn = Z[n];
+    an = act ? A[n * J + c] : 0.0;
+    bn = act ? B[n * J + c] : 0.0;
+  };
+  if (cnt > 0) load(0);
+  for (int i = 0; i < trips; ++i) {
+    const bool live    = i < cnt;
+    const int64_t n    = live ? row(i) : 0;
+    const double t_cur = tn, t_oth = to, a_c = live ? an : 0.0, b_c = live ? bn : 0.0, y = yn, zold = zn;
+    if (i + 1 < cnt) load(i + 1);
+    const bool edge  = LOWER ? (n == 0) : (n == a.N - 1);
+    const double dt  = LOWER ? t_oth - t_cur : t_cur - t_oth;
+    const double p_c = (edge || !live) ? 1.0 : exp(cc * dt);
+    if (F && live && act) F[n * J + c] = Fc;
+    Fc             = p_c * Fc;
+    const double s = gsum<G>(a_c * Fc);
+    double z, r;
+    if (SOLVE) {
+      z = y - s;
+      r = z;
+    } else {
+      z = zold + s;
+      r = y;
+    }
+    if (live && c == 0) Z[n] = z;
+    Fc = fma(b_c, r, Fc);
+  }
+}
+
+// ---- forward summary, solves: lane q carries column q ----------------------------------------------------------------
+template <int J, bool LOWER>
+__global__ void __launch_bounds__(kGroupThreadsS) gsweep_summary_kernel(SweepArgs a) {
+  constexpr int G  = GroupOf<J + 1>::G;  // J + 1 columns
+  constexpr int GP = kGroupThreadsS / G;
+  const int q         = threadIdx.x & (G - 1);
+  const int64_t unit  = (int64_t)blockIdx.x * GP + threadIdx.x / G;
+  const bool has      = unit < a.batch * a.C;
+  const bool act      = has && q < J;  // lanes that also fetch an element of the rows
+  const int64_t chunk = has ? unit % a.C : 0, b = has ? unit / a.C : 0;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
+  const double *t     = a.t + b * a.t_bs;
+  const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
+  const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
+  double Gq[J];
+#pragma unroll
+  for (int j = 0; j < J; ++j) Gq[j] = (j == q) ? 1.0 : 0.0;
+  const int cnt   = (int)(n1 - n0);
+  const int trips = warp_max(cnt);
+  auto row = [&](int i) { return LOWER ? n0 + i : n1 - 1 - i; };
+  double tn = 0.0, to = 0.0, an = 0.0, bn = 0.0, yn = 0.0;
+  auto load = [&](int i) {
+    const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
+    tn = t[n];
+    to = (o >= 0 && o < a.N) ? t[o] : tn;
+    yn = Y[n];
+    an = act ? A[n * J + q] : 0.0;
+    bn = act ? B[n * J + q] : 0.0;
+  };
+  if (cnt > 0) load(0);
+  for (int i = 0; i < trips; ++i) {
+    const bool live    = i < cnt;
+    const int64_t n    = live ? row(i) : 0;
+    const double t_cur = tn, t_oth = to, a_q = live ? an : 0.0, b_q = live ? bn : 0.0, y = live ? yn : 0.0;
+    if (i + 1 < cnt) load(i + 1);
+    const bool edge  = LOWER ? (n == 0) : (n == a.N - 1);
+    const double dt  = LOWER ? t_oth - t_cur : t_cur - t_oth;
+    const double p_q = (edge || !live) ? 1.0 : exp(cc * dt);
+    double p[J], av[J], bv[J];
+    gall<G, J>(p_q, p);
+    gall<G, J>(a_q, av);
+    gall<G, J>(b_q, bv);
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      Gq[j] = p[j] * Gq[j];
+      s     = fma(av[j], Gq[j], s);
+    }
+    const double r = (q == J ? y : 0.0) - s;
+#pragma unroll
+    for (int j = 0; j < J; ++j) Gq[j] = fma(bv[j], r, Gq[j]);
+  }
+  if (has && q <= J) {
+    const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
+    double *e          = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J * J + J);
+    if (q < J) {
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[j * J + q] = Gq[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[J * J + j] = Gq[j];
+    }
+  }
+}
+
+// ---- reverse apply -----------------------------------------------------------------------------------------------------
+template <int J, bool SOLVE, bool LOWER>
+__global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_apply_kernel(SweepRevArgs a) {
+  constexpr int G  = GroupOf<J>::G;
+  constexpr int GP = kGroupThreadsS / G;
+  const int c         = threadIdx.x & (G - 1);
+  const int64_t unit  = (int64_t)blockIdx.x * GP + threadIdx.x / G;
+  const bool has      = unit < a.batch * a.C;
+  const bool act      = has && c < J;
+  const int64_t chunk = has ? unit % a.C : 0, b = has ? unit / a.C : 0;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
+  const double *t     = a.t + b * a.t_bs;
+  const int64_t NJ    = a.N * J;
+  const double *A = a.A + b * NJ, *B = a.B + b * NJ, *F = a.F + b * NJ, *bZ = a.bZ + b * a.N;
+  const double *ZY = SOLVE ? a.Z + b * a.N : a.Y + b * a.y_bs;
+  double *bt = a.bt + b * a.N, *bA = a.bA + b * NJ, *bB = a.bB + b * NJ, *bY = a.bY + b * a.N;
+  const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
+  double bF = 0.0, bc_acc = 0.0, pend = 0.0;
+  if (a.carry && act) {
+    const int64_t leaf = LOWER ? a.C - 1 - chunk : chunk;
+    bF                 = a.carry[(b * a.node_stride + leaf) * (int64_t)J + c];
+  }
+  const double sgn = LOWER ? 1.0 : -1.0;
+  const int cnt    = (int)(n1 - n0);
+  const int trips  = warp_max(cnt);
+  auto row = [&](int i) { return LOWER ? n1 - 1 - i : n0 + i; };
+  double tn = 0.0, to = 0.0, an = 0.0, bn = 0.0, fn = 0.0, bzn = 0.0, zyn = 0.0;
+  auto load = [&](int i) {
+    const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
+    const bool nb   = o >= 0 && o < a.N;
+    tn  = t[n];
+    to  = nb ? t[o] : tn;
+    bzn = bZ[n];
+    zyn = ZY[n];
+    an  = act ? A[n * J + c] : 0.0;
+    bn  = act ? B[n * J + c] : 0.0;
+    fn  = (act && nb) ? F[n * J + c] : 0.0;
+  };
+  if (cnt > 0) load(0);
+  for (int i = 0; i < trips; ++i) {
+    const bool live    = i < cnt;
+    const int64_t n    = live ? row(i) : 0;
+    const int64_t o    = LOWER ? n - 1 : n + 1;
+    const bool nb      = live && o >= 0 && o < a.N;
+    const double t_cur = tn, t_oth = to, a_c = an, b_c = bn, Fn = fn, bz0 = bzn, zy = zyn;
+    if (i + 1 < cnt) load(i + 1);
+    const double dot = gsum<G>(b_c * bF);
+    double bz;
+    if (SOLVE) {
+      bz = bz0 + dot;
+      if (live && c == 0) bY[n] = bz;
+    } else {
+      bz = bz0;
+      if (live && c == 0) bY[n] = dot;
+    }
+    if (live && act) bB[n * J + c] = zy * bF;
+    const double dt  = sgn * (t_oth - t_cur);
+    const double p_c = nb ? exp(cc * dt) : 1.0;
+    const double au  = a_c * bz;
+    const double nf  = SOLVE ? bF - au : bF + au;
+    const double pf  = p_c * Fn;
+    const double bp  = Fn * nf * p_c;
+    const double fac = gsum<G>(cc * bp);
+    if (nb) {
+      if (act) bA[n * J + c] = SOLVE ? -(bz * pf) : bz * pf;
+      bc_acc = fma(dt, bp, bc_acc);
+      if (c == 0) bt[n] = pend - sgn * fac;
+      pend = sgn * fac;
+      bF   = p_c * nf;
+    } else if (live) {
+      if (act) bA[n * J + c] = 0.0;
+      if (c == 0) bt[n] = pend;
+      pend = 0.0;
+    }
+  }
+  if (act) a.bc_part[(b * a.C + chunk) * J + c] = bc_acc;
+  if (has && c == 0) a.bt_edge[b * a.C + chunk] = pend;
+}
+
+// ---- reverse summary, solves -----------------------------------------------------------------------------------------
+template <int J, bool LOWER>
+__global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_summary_kernel(SweepRevArgs a) {
+  constexpr int G  = GroupOf<J + 1>::G;
+  constexpr int GP = kGroupThreadsS / G;
+  const int q         = threadIdx.x & (G - 1);
+  const int64_t unit  = (int64_t)blockIdx.x * GP + threadIdx.x / G;
+  const bool has      = unit < a.batch * a.C;
+  const bool act      = has && q < J;
+  const int64_t chunk = has ? unit % a.C : 0, b = has ? unit / a.C : 0;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
+  const double *t     = a.t + b * a.t_bs;
+  const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *bZ = a.bZ + b * a.N;
+  const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
+  double Gq[J];
+#pragma unroll
+  for (int j = 0; j < J; ++j) Gq[j] = (j == q) ? 1.0 : 0.0;
+  const double sgn = LOWER ? 1.0 : -1.0;
+  const int cnt    = (int)(n1 - n0);
+  const int trips  = warp_max(cnt);
+  auto row = [&](int i) { return LOWER ? n1 - 1 - i : n0 + i; };
+  double tn = 0.0, to = 0.0, an = 0.0, bn = 0.0, bzn = 0.0;
+  auto load = [&](int i) {
+    const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
+    tn  = t[n];
+    to  = (o >= 0 && o < a.N) ? t[o] : tn;
+    bzn = bZ[n];
+    an  = act ? A[n * J + q] : 0.0;
+    bn  = act ? B[n * J + q] : 0.0;
+  };
+  if (cnt > 0) load(0);
+  for (int i = 0; i < trips; ++i) {
+    const bool live    = i < cnt;
+    const int64_t n    = live ? row(i) : 0;
+    const int64_t o    = LOWER ? n - 1 : n + 1;
+    const bool nb      = live && o >= 0 && o < a.N;
+    const double t_cur = tn, t_oth = to, a_q = an, b_q = bn, bz0 = bzn;
+    if (i + 1 < cnt) load(i + 1);
+    const double p_q = nb ? exp(cc * sgn * (t_oth - t_cur)) : 1.0;
+    double p[J], av[J], bv[J];
+    gall<G, J>(p_q, p);
+    gall<G, J>(a_q, av);
+    gall<G, J>(b_q, bv);
+    if (nb) {
+      double bz = (q == J) ? bz0 : 0.0;
+#pragma unroll
+      for (int j = 0; j < J; ++j) bz = fma(bv[j], Gq[j], bz);
+#pragma unroll
+      for (int j = 0; j < J; ++j) Gq[j] = p[j] * fma(-av[j], bz, Gq[j]);
+    }
+  }
+  if (has && q <= J) {
+    const int64_t leaf = LOWER ? a.C - 1 - chunk : chunk;
+    double *e          = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J * J + J);
+    if (q < J) {
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[j * J + q] = Gq[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[J * J + j] = Gq[j];
+    }
+  }
+}
+
+}  // namespace c2b

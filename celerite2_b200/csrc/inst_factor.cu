@@ -4,6 +4,7 @@
 #include "host_common.cuh"
 #include "factor.cuh"
 #include "fast_factor.cuh"
+#include "gfactor.cuh"
 
 #ifndef C2B_JT
 #error "compile with -DC2B_JT=<width> (0 = run-time width)"
@@ -34,8 +35,28 @@ static int launch_factor_fast(FactorArgs &g, const ScanBuffers &sb, cudaStream_t
   return C2B_OK;
 }
 
+// compile-time widths up to 8: lane-group kernels (gfactor.cuh)
+template <int JT>
+static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 8) {
+    constexpr int GP    = kGroupThreads / GroupOf<JT>::G;
+    const unsigned grid = (unsigned)((g.batch * g.C + GP - 1) / GP);
+    if (g.C > 1) {
+      g.leaves      = sb.nodes;
+      g.node_stride = sb.node_stride;
+      C2B_LAUNCH("gfactor_summary_kernel", stream, gfactor_summary_kernel<JT><<<grid, kGroupThreads, 0, stream>>>(g));
+      int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      g.carry = sb.states;
+    }
+    C2B_LAUNCH("gfactor_apply_kernel", stream, gfactor_apply_kernel<JT><<<grid, kGroupThreads, 0, stream>>>(g));
+  }
+  return C2B_OK;
+}
+
 template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
+  if (JT > 0 && JT <= 8 && !getenv("C2B_NO_GROUP")) return launch_factor_group<JT>(g, sb, stream);
   if (JT > 0 && getenv("C2B_TMA")) return launch_factor_fast<JT>(g, sb, stream);  // experimental, see DESIGN.md
   unsigned grid, block;
   size_t smem;

@@ -1,6 +1,9 @@
 // Launchers of the sweep kernels for ONE compile-time width (C2B_JT); see args.cuh.
 #include "host_common.cuh"
+#include <stdlib.h>
+
 #include "sweep.cuh"
+#include "gsweep.cuh"
 
 #ifndef C2B_JT
 #error "compile with -DC2B_JT=<width> (0 = run-time width)"
@@ -8,8 +11,52 @@
 
 namespace c2b {
 
+// K == 1 solves with a compile-time width up to 8: lane-group kernels (gsweep.cuh)
+template <int JT, bool SOLVE, bool LOWER>
+static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 8 && SOLVE) {
+    if (a.C > 1) {
+      a.leaves      = sb.nodes;
+      a.node_stride = sb.node_stride;
+      constexpr int GPS   = kGroupThreadsS / GroupOf<JT + 1>::G;
+      const unsigned grid = (unsigned)((a.batch * a.C + GPS - 1) / GPS);
+      C2B_LAUNCH("gsweep_summary_kernel", stream, gsweep_summary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      int rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      a.carry = sb.states;
+    }
+    constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
+    const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
+    C2B_LAUNCH("gsweep_apply_kernel", stream, gsweep_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+  }
+  return C2B_OK;
+}
+
+template <int JT, bool SOLVE, bool LOWER>
+static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 8 && SOLVE) {
+    if (a.C > 1) {
+      a.leaves      = sb.nodes;
+      a.node_stride = sb.node_stride;
+      constexpr int GPS   = kGroupThreadsS / GroupOf<JT + 1>::G;
+      const unsigned grid = (unsigned)((a.batch * a.C + GPS - 1) / GPS);
+      C2B_LAUNCH("gsweep_rev_summary_kernel", stream, gsweep_rev_summary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      int rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      a.carry = sb.states;
+    }
+    constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
+    const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
+    C2B_LAUNCH("gsweep_rev_apply_kernel", stream, gsweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+    C2B_LAUNCH("rev_finalize_kernel", stream,
+               rev_finalize_kernel<<<(unsigned)a.batch, 256, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc));
+  }
+  return C2B_OK;
+}
+
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
@@ -43,6 +90,8 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
 
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
+  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && !getenv("C2B_NO_GROUP"))
+    return launch_sweep_rev_group<JT, SOLVE, LOWER>(a, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
