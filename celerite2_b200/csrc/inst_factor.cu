@@ -5,6 +5,7 @@
 #include "factor.cuh"
 #include "fast_factor.cuh"
 #include "gfactor.cuh"
+#include "gfactor_rev.cuh"
 
 #ifndef C2B_JT
 #error "compile with -DC2B_JT=<width> (0 = run-time width)"
@@ -78,7 +79,28 @@ int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
 }
 
 template <int JT>
+static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 8) {
+    constexpr int GP    = kGroupThreadsR / GroupOf<JT>::G;
+    const unsigned grid = (unsigned)((g.batch * g.C + GP - 1) / GP);
+    if (g.C > 1) {
+      g.leaves      = sb.nodes;
+      g.node_stride = sb.node_stride;
+      C2B_LAUNCH("gfactor_rev_summary_kernel", stream, gfactor_rev_kernel<JT, false><<<grid, kGroupThreadsR, 0, stream>>>(g));
+      int rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      g.carry = sb.states;
+    }
+    C2B_LAUNCH("gfactor_rev_apply_kernel", stream, gfactor_rev_kernel<JT, true><<<grid, kGroupThreadsR, 0, stream>>>(g));
+    C2B_LAUNCH("rev_finalize_kernel", stream,
+               rev_finalize_kernel<<<(unsigned)g.batch, 256, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc));
+  }
+  return C2B_OK;
+}
+
+template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
+  if (JT > 0 && JT <= 8 && !getenv("C2B_NO_GROUP")) return launch_factor_rev_group<JT>(g, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
