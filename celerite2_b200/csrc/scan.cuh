@@ -152,83 +152,60 @@ C2B_DEV void wdown_node(int lane, int J, int K, const Levels &lv, const double *
   __syncwarp();
 }
 
-constexpr int kCoopLeaves = 32;  // leaves per warp block
+constexpr int kCoopLeaves = 32;  // nodes per block
 constexpr int kCoopLevels = 5;
+constexpr int kCoopWarps  = 16;  // warps per CTA: one combine each, so a tree level of a block is one round
 
+// One CTA per (series, block of 32 nodes at level `lb`): builds levels lb+1 .. min(lb+5, top).  Every level is one
+// round of independent warp-cooperative combines, separated by CTA barriers.
 template <class Mon>
-__global__ void scan_up_coop(int J_, int K, int64_t batch, Levels lv, double *nodes_all) {
-  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
+__global__ void __launch_bounds__(kCoopWarps * 32) scan_up_block(int J_, int K, int64_t batch, Levels lv, int lb, double *nodes_all) {
+  const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ double sm_all[];
   const int wsm      = Coop<Mon>::wsmem(J, K);
   const int wib      = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *sm         = sm_all + (size_t)wib * wsm;
-  const int64_t nblk = (lv.count[0] + kCoopLeaves - 1) / kCoopLeaves;
-  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-  if (warp >= batch * nblk) return;
-  const int64_t b = warp / nblk, blk = warp % nblk;
+  const int64_t nblk = (lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves;
+  const int64_t b = blockIdx.x / nblk, blk = blockIdx.x % nblk;
   const int es  = Mon::esize(J, K);
   double *nodes = nodes_all + b * lv.total * es;
-  const int top = lv.nlev - 1 < kCoopLevels ? lv.nlev - 1 : kCoopLevels;
-  for (int l = 1; l <= top; ++l) {
-    const int64_t first = (blk * kCoopLeaves) >> l;
-    for (int r = 0; r < (kCoopLeaves >> l); ++r)
+  const int top = lv.nlev - 1 < lb + kCoopLevels ? lv.nlev - 1 : lb + kCoopLevels;
+  for (int l = lb + 1; l <= top; ++l) {
+    const int sh        = l - lb;
+    const int64_t first = (blk * kCoopLeaves) >> sh;
+    for (int r = wib; r < (kCoopLeaves >> sh); r += kCoopWarps)
       if (first + r < lv.count[l]) wup_node<Mon>(lane, J, K, lv, nodes, es, l, first + r, sm);
-    __syncwarp();
-  }
-}
-
-template <class Mon>
-__global__ void __launch_bounds__(512) scan_top_coop(int J_, int K, Levels lv, double *nodes_all, double *states_all, const double *init) {
-  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
-  extern __shared__ double sm_all[];
-  const int wsm  = Coop<Mon>::wsmem(J, K);
-  const int wib  = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-  double *sm     = sm_all + (size_t)wib * wsm;
-  const int64_t b = blockIdx.x;
-  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
-  double *nodes  = nodes_all + b * lv.total * es;
-  double *states = states_all + b * lv.total * ss;
-  const int top  = lv.nlev - 1;
-  for (int l = kCoopLevels + 1; l <= top; ++l) {
-    for (int64_t idx = wib; idx < lv.count[l]; idx += nw) wup_node<Mon>(lane, J, K, lv, nodes, es, l, idx, sm);
-    __syncthreads();
-  }
-  {
-    double *st = states + lv.off[top] * ss;
-    for (int i = threadIdx.x; i < ss; i += blockDim.x) st[i] = init ? init[b * ss + i] : 0.0;
-  }
-  __syncthreads();
-  for (int l = top; l > kCoopLevels; --l) {
-    for (int64_t idx = wib; idx < lv.count[l]; idx += nw) wdown_node<Mon>(lane, J, K, lv, nodes, states, es, ss, l, idx, sm);
     __syncthreads();
   }
 }
 
+// Mirror image: states of levels min(lb+5, top) .. lb+1 are pushed down to level lb.  The CTA that owns the top of the
+// tree seeds it with the initial state.
 template <class Mon>
-__global__ void scan_down_coop(int J_, int K, int64_t batch, Levels lv, const double *nodes_all, double *states_all, const double *init) {
-  const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
+__global__ void __launch_bounds__(kCoopWarps * 32) scan_down_block(int J_, int K, int64_t batch, Levels lv, int lb,
+                                                                    const double *nodes_all, double *states_all, const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ double sm_all[];
   const int wsm      = Coop<Mon>::wsmem(J, K);
   const int wib      = threadIdx.x >> 5, lane = threadIdx.x & 31;
   double *sm         = sm_all + (size_t)wib * wsm;
-  const int64_t nblk = (lv.count[0] + kCoopLeaves - 1) / kCoopLeaves;
-  const int64_t warp = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-  if (warp >= batch * nblk) return;
-  const int64_t b = warp / nblk, blk = warp % nblk;
+  const int64_t nblk = (lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves;
+  const int64_t b = blockIdx.x / nblk, blk = blockIdx.x % nblk;
   const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
   const double *nodes = nodes_all + b * lv.total * es;
   double *states      = states_all + b * lv.total * ss;
-  const int top       = lv.nlev - 1 < kCoopLevels ? lv.nlev - 1 : kCoopLevels;
-  if (lv.nlev - 1 <= kCoopLevels) {
+  const int top       = lv.nlev - 1 < lb + kCoopLevels ? lv.nlev - 1 : lb + kCoopLevels;
+  if (top == lv.nlev - 1) {
     double *st = states + lv.off[top] * ss;
-    for (int i = lane; i < ss; i += 32) st[i] = init ? init[b * ss + i] : 0.0;
-    __syncwarp();
+    for (int i = threadIdx.x; i < ss; i += blockDim.x) st[i] = init ? init[b * ss + i] : 0.0;
+    __syncthreads();
   }
-  for (int l = top; l >= 1; --l) {
-    const int64_t first = (blk * kCoopLeaves) >> l;
-    for (int r = 0; r < (kCoopLeaves >> l); ++r)
+  for (int l = top; l > lb; --l) {
+    const int sh        = l - lb;
+    const int64_t first = (blk * kCoopLeaves) >> sh;
+    for (int r = wib; r < (kCoopLeaves >> sh); r += kCoopWarps)
       if (first + r < lv.count[l]) wdown_node<Mon>(lane, J, K, lv, nodes, states, es, ss, l, first + r, sm);
-    __syncwarp();
+    __syncthreads();
   }
 }
 
@@ -247,18 +224,27 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop) {
-    const int wsm       = Coop<Mon>::wsmem(J, K);
-    const size_t smem1  = (size_t)wsm * sizeof(double);  // one warp per CTA: spreads the blocks over all SMs
-    const unsigned grid = (unsigned)(batch * nblk);
-    if (lv.nlev > 1) C2B_LAUNCH("scan_up_coop", stream, scan_up_coop<Mon><<<grid, 32, smem1, stream>>>(J, K, batch, lv, nodes));
-    if (lv.nlev - 1 > kCoopLevels) {
-      const int nw = 16;  // 512 threads: leaves 128 registers per thread for the private elimination
-      if ((size_t)nw * smem1 > 48 * 1024)
-        C2B_CUDA(cudaFuncSetAttribute(scan_top_coop<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)((size_t)nw * smem1)));
-      C2B_LAUNCH("scan_top_coop", stream,
-                 scan_top_coop<Mon><<<(unsigned)batch, nw * 32, (size_t)nw * smem1, stream>>>(J, K, lv, nodes, states, init));
+    const int wsm     = Coop<Mon>::wsmem(J, K);
+    const size_t smem = (size_t)kCoopWarps * wsm * sizeof(double);
+    if (smem > 48 * 1024) {
+      C2B_CUDA(cudaFuncSetAttribute(scan_up_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      C2B_CUDA(cudaFuncSetAttribute(scan_down_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
-    C2B_LAUNCH("scan_down_coop", stream, scan_down_coop<Mon><<<grid, 32, smem1, stream>>>(J, K, batch, lv, nodes, states, init));
+    const int top = lv.nlev - 1;
+    int bases[kMaxLevels], nb = 0;
+    for (int lb = 0; lb < top || nb == 0; lb += kCoopLevels) bases[nb++] = lb;
+    for (int q = 0; q < nb; ++q) {
+      const int lb        = bases[q];
+      const unsigned grid = (unsigned)(batch * ((lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves));
+      if (lb < top)
+        C2B_LAUNCH("scan_up_block", stream, scan_up_block<Mon><<<grid, kCoopWarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes));
+    }
+    for (int q = nb - 1; q >= 0; --q) {
+      const int lb        = bases[q];
+      const unsigned grid = (unsigned)(batch * ((lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves));
+      C2B_LAUNCH("scan_down_block", stream,
+                 scan_down_block<Mon><<<grid, kCoopWarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes, states, init));
+    }
     return C2B_OK;
   } else {
   const int threads  = 128;  // 4 warps
