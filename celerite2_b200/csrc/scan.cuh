@@ -261,30 +261,36 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   }
 }
 
-// Finalise a reverse op: add the bt term each chunk owes its neighbour and reduce the per-chunk bc partials in
-// a fixed order (deterministic).  One CTA per series.
+// Finalise a reverse op: add the bt term each chunk owes its neighbour (one thread per chunk) and, in the first CTA
+// of every series, reduce the per-chunk bc partials in a fixed order (deterministic).  grid = (ceil(C/1024), batch).
 //   descending == true  (lower / factor_rev): chunk k owes bt[n0_k - 1]
 //   descending == false (upper)             : chunk k owes bt[n1_k]
-static __global__ void rev_finalize_kernel(int64_t N, int64_t C, int64_t L, int J, bool descending, const double *bc_part,
-                                    const double *bt_edge, double *bt, double *bc) {
-  const int64_t b = blockIdx.x;
-  for (int64_t k = threadIdx.x; k < C; k += blockDim.x) {
+static __global__ void __launch_bounds__(1024) rev_finalize_kernel(int64_t N, int64_t C, int64_t L, int J, bool descending,
+                                                                   const double *bc_part, const double *bt_edge, double *bt, double *bc) {
+  const int64_t b = blockIdx.y;
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < C) {
     const int64_t n0 = k * L, n1 = (n0 + L < N) ? n0 + L : N;
     const int64_t tgt = descending ? n0 - 1 : n1;
     if (tgt >= 0 && tgt < N) bt[b * N + tgt] += bt_edge[b * C + k];
   }
-  // bc[j] = sum over chunks, fixed tree order
-  __shared__ double sh[256];
+  if (blockIdx.x != 0) return;
+  // bc[j] = sum over chunks: strided partial sums per thread, then a fixed-shape tree
+  __shared__ double sh[32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
   for (int j = 0; j < J; ++j) {
     double s = 0.0;
-    for (int64_t k = threadIdx.x; k < C; k += blockDim.x) s += bc_part[(b * C + k) * J + j];
-    sh[threadIdx.x] = s;
+    for (int64_t q = threadIdx.x; q < C; q += blockDim.x) s += bc_part[(b * C + q) * J + j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) sh[wid] = s;
     __syncthreads();
-    for (int w = blockDim.x / 2; w > 0; w >>= 1) {
-      if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
-      __syncthreads();
+    if (wid == 0) {
+      double v = lane < nw ? sh[lane] : 0.0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) bc[b * J + j] = v;
     }
-    if (threadIdx.x == 0) bc[b * J + j] = sh[0];
     __syncthreads();
   }
 }
