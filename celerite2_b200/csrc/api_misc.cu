@@ -316,7 +316,7 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
   const int nred    = Jr + 3 * Jc;
   dim3 grid((unsigned)g.ctas_per_series, (unsigned)batch);
   C2B_LAUNCH("assemble_rev_kernel", stream, assemble_rev_kernel<<<grid, kAsmRevThreads, (size_t)nred * kAsmRevThreads * sizeof(double), stream>>>(g));
-  C2B_LAUNCH("assemble_rev_final_kernel", stream, assemble_rev_final_kernel<<<(unsigned)batch, 64, 0, stream>>>(g));
+  C2B_LAUNCH("assemble_rev_final_kernel", stream, assemble_rev_final_kernel<<<(unsigned)batch, 256, 0, stream>>>(g));
   return C2B_OK;
 }
 
@@ -334,7 +334,7 @@ int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, 
   const int ctas = red_ctas(N);
   dim3 grid((unsigned)ctas, (unsigned)batch);
   C2B_LAUNCH("norm_logdet_kernel", stream, norm_logdet_kernel<<<grid, kRedThreads, 0, stream>>>(N, d, z, bz, bd, (double *)sc.ptr, ctas));
-  C2B_LAUNCH("norm_logdet_final_kernel", stream, norm_logdet_final_kernel<<<(unsigned)batch, 32, 0, stream>>>((const double *)sc.ptr, ctas, out));
+  C2B_LAUNCH("norm_logdet_final_kernel", stream, norm_logdet_final_kernel<<<(unsigned)batch, 64, 0, stream>>>((const double *)sc.ptr, ctas, out));
   return C2B_OK;
 }
 

@@ -108,20 +108,26 @@ __global__ void assemble_rev_kernel(AsmRevArgs g) {
 }
 
 __global__ void assemble_rev_final_kernel(AsmRevArgs g) {
+  // one warp per reduced quantity: lanes stride over the per-CTA partials, fixed-shape shuffle tree (deterministic)
   const int J     = g.Jr + 2 * g.Jc;
   const int nred  = g.Jr + 3 * g.Jc;
   const int64_t b = blockIdx.x;
-  for (int r = threadIdx.x; r < nred; r += blockDim.x) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (int r = wid; r < nred; r += nw) {
     double s = 0.0;
-    for (int k = 0; k < g.ctas_per_series; ++k) s += g.part[(b * g.ctas_per_series + k) * nred + r];
-    if (r < g.Jr)
-      g.b_ar[b * g.Jr + r] = s;
-    else if (r < g.Jr + g.Jc)
-      g.b_ac[b * g.Jc + (r - g.Jr)] = s;
-    else if (r < g.Jr + 2 * g.Jc)
-      g.b_bc[b * g.Jc + (r - g.Jr - g.Jc)] = s;
-    else
-      g.b_dc[b * g.Jc + (r - g.Jr - 2 * g.Jc)] = s;
+    for (int k = lane; k < g.ctas_per_series; k += 32) s += g.part[(b * g.ctas_per_series + k) * nred + r];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+      if (r < g.Jr)
+        g.b_ar[b * g.Jr + r] = s;
+      else if (r < g.Jr + g.Jc)
+        g.b_ac[b * g.Jc + (r - g.Jr)] = s;
+      else if (r < g.Jr + 2 * g.Jc)
+        g.b_bc[b * g.Jc + (r - g.Jr - g.Jc)] = s;
+      else
+        g.b_dc[b * g.Jc + (r - g.Jr - 2 * g.Jc)] = s;
+    }
   }
   const double *b_c = g.b_c ? g.b_c + b * J : nullptr;
   for (int j = threadIdx.x; j < g.Jr; j += blockDim.x) g.b_cr[b * g.Jr + j] = b_c ? b_c[j] : 0.0;
@@ -159,11 +165,15 @@ __global__ void norm_logdet_kernel(int64_t N, const double *d, const double *z, 
   }
 }
 __global__ void norm_logdet_final_kernel(const double *part, int ctas, double *out) {
+  // warp 0: log-det, warp 1: chi^2
   const int64_t b = blockIdx.x;
-  if (threadIdx.x < 2) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (wid < 2) {
     double s = 0.0;
-    for (int k = 0; k < ctas; ++k) s += part[(b * ctas + k) * 2 + threadIdx.x];
-    out[b * 2 + threadIdx.x] = s;
+    for (int k = lane; k < ctas; k += 32) s += part[(b * ctas + k) * 2 + wid];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) out[b * 2 + wid] = s;
   }
 }
 
