@@ -309,9 +309,14 @@ def run_ours(args):
     dom_bytes = bpp[dom] * N
     achieved = dom_bytes / (per_op[dom] * 1e-3) / 1e9
     step_bytes = sum(bpp.values()) * N
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if cfg["name"] == "c2" and os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get(dom)  # DRAM bytes per call from the committed ncu --set full captures
     roofline = {
         "bound": "hbm", "kernel": dom + " (all kernels of the C-ABI call: summary + scan + apply)",
-        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
         "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": per_op[dom],
         "whole_step": {"algorithmic_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,
                        "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
