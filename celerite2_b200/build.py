@@ -20,7 +20,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 # (source, width or None).  The width lists must match C2B_DISPATCH_J_* in csrc/host_common.cuh.
 WIDTHS_SWEEP = [0, 2, 4, 6, 16]
-WIDTHS_FACTOR = [0, 2, 4, 6]
+WIDTHS_FACTOR = [0, 2, 4, 6, 16]
 UNITS = (
     [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_pipeline.cu", None), ("api_noalloc.cu", None)]
     + [("inst_sweep.cu", w) for w in WIDTHS_SWEEP]

@@ -279,4 +279,93 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_summary_kernel(Swee
   }
 }
 
+// =================================================================================================================
+// Multi-right-hand-side solves (K > 1): one warp per (series, chunk, tile of 32 columns); lane k of the warp
+// carries the J-vector state of ITS column, so the columns never talk to each other.  The row's A / B entries and
+// exp(c dt) are fetched / evaluated once per row by lanes 0..J-1 and broadcast with shuffles.  Y and Z accesses
+// are coalesced across the lanes.  Summary: the same kernel over J + K columns (J unit vectors, then the real ones).
+// =================================================================================================================
+template <int J, bool LOWER, bool SUMMARY>
+__global__ void __launch_bounds__(128) csweep_kernel(SweepArgs a) {
+  static_assert(J <= 32, "one lane per row element");
+  const int lane       = threadIdx.x & 31;
+  const int ncol       = SUMMARY ? J + a.K : a.K;
+  const int tiles      = (ncol + 31) / 32;
+  const int64_t warp   = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (warp >= a.batch * a.C * tiles) return;  // whole warps only
+  const int tile       = (int)(warp % tiles);
+  const int64_t chunk  = (warp / tiles) % a.C;
+  const int64_t b      = warp / ((int64_t)tiles * a.C);
+  const int64_t n0     = chunk * a.L;
+  const int64_t n1     = n0 + a.L < a.N ? n0 + a.L : a.N;
+  const int q          = tile * 32 + lane;  // my column
+  const bool have      = q < ncol;
+  const bool basis     = SUMMARY && q < J;
+  const int k          = SUMMARY ? q - J : q;  // real column index
+  const double *t      = a.t + b * a.t_bs;
+  const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J;
+  const double *Y = a.Y + b * a.y_bs;
+  double *Z = a.Z + b * a.N * (int64_t)a.K;
+  double *F = (!SUMMARY && a.F) ? a.F + b * a.N * (int64_t)J * a.K : nullptr;
+  const double cc = lane < J ? (a.c + b * a.c_bs)[lane] : 0.0;
+  const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
+  double Fk[J];
+#pragma unroll
+  for (int j = 0; j < J; ++j) Fk[j] = (basis && j == q) ? 1.0 : 0.0;
+  if (!SUMMARY && a.carry && have) {
+    const double *st = a.carry + (b * a.node_stride + leaf) * (int64_t)(J * a.K) + (int64_t)J * k;
+#pragma unroll
+    for (int j = 0; j < J; ++j) Fk[j] = st[j];
+  }
+  const int cnt = (int)(n1 - n0);
+  auto row = [&](int i) { return LOWER ? n0 + i : n1 - 1 - i; };
+  double tn = 0.0, to = 0.0, an = 0.0, bn = 0.0, yn = 0.0;
+  auto load = [&](int i) {
+    const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
+    tn = t[n];
+    to = (o >= 0 && o < a.N) ? t[o] : tn;
+    an = lane < J ? A[n * J + lane] : 0.0;
+    bn = lane < J ? B[n * J + lane] : 0.0;
+    yn = (have && !basis) ? Y[n * (int64_t)a.K + k] : 0.0;
+  };
+  if (cnt > 0) load(0);
+  for (int i = 0; i < cnt; ++i) {
+    const int64_t n    = row(i);
+    const double t_cur = tn, t_oth = to, a_l = an, b_l = bn, y = yn;
+    if (i + 1 < cnt) load(i + 1);
+    const bool edge  = LOWER ? (n == 0) : (n == a.N - 1);
+    const double dt  = LOWER ? t_oth - t_cur : t_cur - t_oth;
+    const double p_l = edge ? 1.0 : exp(cc * dt);
+    if (F && have) {
+#pragma unroll
+      for (int j = 0; j < J; ++j) F[n * (int64_t)J * a.K + (int64_t)J * k + j] = Fk[j];
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      const double pj = __shfl_sync(0xffffffffu, p_l, j);
+      const double aj = __shfl_sync(0xffffffffu, a_l, j);
+      Fk[j]           = pj * Fk[j];
+      s               = fma(aj, Fk[j], s);
+    }
+    const double z = y - s;
+    if (!SUMMARY && have) Z[n * (int64_t)a.K + k] = z;
+#pragma unroll
+    for (int j = 0; j < J; ++j) {
+      const double bj = __shfl_sync(0xffffffffu, b_l, j);
+      Fk[j]           = fma(bj, z, Fk[j]);
+    }
+  }
+  if (SUMMARY && have) {
+    double *e = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J * J + J * a.K);
+    if (basis) {
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[j * J + q] = Fk[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[J * J + j + J * k] = Fk[j];
+    }
+  }
+}
+
 }  // namespace c2b

@@ -20,6 +20,7 @@ namespace c2b {
     case 2: CALL(2); break;                                                                                                               \
     case 4: CALL(4); break;                                                                                                               \
     case 6: CALL(6); break;                                                                                                               \
+    case 16: CALL(16); break;                                                                                                             \
     default: CALL(0); break;                                                                                                              \
   }
 

@@ -16,7 +16,7 @@ namespace c2b {
 // compile-time widths: TMA tile pipeline (fast_factor.cuh)
 template <int JT>
 static int launch_factor_fast(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
-  if constexpr (JT > 0) {
+  if constexpr (JT > 0 && JT <= 8) {
     using Lay = FFactorLayout<JT>;
     const unsigned grid = (unsigned)((g.batch * g.C + 31) / 32);
     if (g.C > 1) {
@@ -36,10 +36,10 @@ static int launch_factor_fast(FactorArgs &g, const ScanBuffers &sb, cudaStream_t
   return C2B_OK;
 }
 
-// compile-time widths up to 8: lane-group kernels (gfactor.cuh)
+// compile-time widths up to 16: lane-group kernels (gfactor.cuh)
 template <int JT>
 static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
-  if constexpr (JT > 0 && JT <= 8) {
+  if constexpr (JT > 0 && JT <= 16) {
     constexpr int GP    = kGroupThreads / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((g.batch * g.C + GP - 1) / GP);
     if (g.C > 1) {
@@ -57,7 +57,7 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
 
 template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
-  if (JT > 0 && JT <= 8 && !getenv("C2B_NO_GROUP")) return launch_factor_group<JT>(g, sb, stream);
+  if (JT > 0 && JT <= 16 && !getenv("C2B_NO_GROUP")) return launch_factor_group<JT>(g, sb, stream);
   if (JT > 0 && getenv("C2B_TMA")) return launch_factor_fast<JT>(g, sb, stream);  // experimental, see DESIGN.md
   unsigned grid, block;
   size_t smem;
@@ -80,7 +80,7 @@ int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
 
 template <int JT>
 static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
-  if constexpr (JT > 0 && JT <= 8) {
+  if constexpr (JT > 0 && JT <= 16) {
     constexpr int GP    = kGroupThreadsR / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((g.batch * g.C + GP - 1) / GP);
     if (g.C > 1) {
@@ -100,7 +100,7 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
 
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
-  if (JT > 0 && JT <= 8 && !getenv("C2B_NO_GROUP")) return launch_factor_rev_group<JT>(g, sb, bc, stream);
+  if (JT > 0 && JT <= 16 && !getenv("C2B_NO_GROUP")) return launch_factor_rev_group<JT>(g, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;

@@ -54,8 +54,28 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
   return C2B_OK;
 }
 
+// K > 1 solves with a compile-time width: one warp per 32 columns (csweep_kernel)
+template <int JT, bool SOLVE, bool LOWER>
+static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if constexpr (JT > 0 && SOLVE) {
+    if (a.C > 1) {
+      a.leaves      = sb.nodes;
+      a.node_stride = sb.node_stride;
+      const int64_t warps = a.batch * a.C * ((JT + a.K + 31) / 32);
+      C2B_LAUNCH("csweep_summary_kernel", stream, csweep_kernel<JT, LOWER, true><<<(unsigned)((warps + 3) / 4), 128, 0, stream>>>(a));
+      int rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      a.carry = sb.states;
+    }
+    const int64_t warps = a.batch * a.C * ((a.K + 31) / 32);
+    C2B_LAUNCH("csweep_apply_kernel", stream, csweep_kernel<JT, LOWER, false><<<(unsigned)((warps + 3) / 4), 128, 0, stream>>>(a));
+  }
+  return C2B_OK;
+}
+
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if (JT > 0 && SOLVE && a.K > 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
   if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
   size_t smem;

@@ -154,7 +154,7 @@ C2B_DEV void wdown_node(int lane, int J, int K, const Levels &lv, const double *
 
 constexpr int kCoopLeaves = 32;  // nodes per block
 constexpr int kCoopLevels = 5;
-constexpr int kCoopWarps  = 16;  // warps per CTA: one combine each, so a tree level of a block is one round
+constexpr int kCoopWarps  = 16;  // warps per CTA (fewer when the per-warp shared memory is large): one combine each per round
 
 // One CTA per (series, block of 32 nodes at level `lb`): builds levels lb+1 .. min(lb+5, top).  Every level is one
 // round of independent warp-cooperative combines, separated by CTA barriers.
@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(kCoopWarps * 32) scan_up_block(int J_, int K, 
   for (int l = lb + 1; l <= top; ++l) {
     const int sh        = l - lb;
     const int64_t first = (blk * kCoopLeaves) >> sh;
-    for (int r = wib; r < (kCoopLeaves >> sh); r += kCoopWarps)
+    for (int r = wib; r < (kCoopLeaves >> sh); r += (int)(blockDim.x >> 5))
       if (first + r < lv.count[l]) wup_node<Mon>(lane, J, K, lv, nodes, es, l, first + r, sm);
     __syncthreads();
   }
@@ -203,7 +203,7 @@ __global__ void __launch_bounds__(kCoopWarps * 32) scan_down_block(int J_, int K
   for (int l = top; l > lb; --l) {
     const int sh        = l - lb;
     const int64_t first = (blk * kCoopLeaves) >> sh;
-    for (int r = wib; r < (kCoopLeaves >> sh); r += kCoopWarps)
+    for (int r = wib; r < (kCoopLeaves >> sh); r += (int)(blockDim.x >> 5))
       if (first + r < lv.count[l]) wdown_node<Mon>(lane, J, K, lv, nodes, states, es, ss, l, first + r, sm);
     __syncthreads();
   }
@@ -225,7 +225,9 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop) {
     const int wsm     = Coop<Mon>::wsmem(J, K);
-    const size_t smem = (size_t)kCoopWarps * wsm * sizeof(double);
+    int nwarps = kCoopWarps;
+    while (nwarps > 1 && (size_t)nwarps * wsm * sizeof(double) > 200 * 1024) nwarps >>= 1;
+    const size_t smem = (size_t)nwarps * wsm * sizeof(double);
     if (smem > 48 * 1024) {
       C2B_CUDA(cudaFuncSetAttribute(scan_up_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       C2B_CUDA(cudaFuncSetAttribute(scan_down_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -237,13 +239,13 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
       const int lb        = bases[q];
       const unsigned grid = (unsigned)(batch * ((lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves));
       if (lb < top)
-        C2B_LAUNCH("scan_up_block", stream, scan_up_block<Mon><<<grid, kCoopWarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes));
+        C2B_LAUNCH("scan_up_block", stream, scan_up_block<Mon><<<grid, nwarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes));
     }
     for (int q = nb - 1; q >= 0; --q) {
       const int lb        = bases[q];
       const unsigned grid = (unsigned)(batch * ((lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves));
       C2B_LAUNCH("scan_down_block", stream,
-                 scan_down_block<Mon><<<grid, kCoopWarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes, states, init));
+                 scan_down_block<Mon><<<grid, nwarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes, states, init));
     }
     return C2B_OK;
   } else {
