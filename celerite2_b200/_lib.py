@@ -38,7 +38,9 @@ for _op in ("solve_lower", "solve_upper", "matmul_lower", "matmul_upper"):
     _SIGS["c2b_" + _op + "_rev"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp]
 
 EXPORTS = sorted(list(_SIGS) + ["c2b_version", "c2b_last_error", "c2b_device_count", "c2b_scratch_bytes", "c2b_set_chunks_per_series",
-                                 "c2b_profile_enable", "c2b_profile_report", "c2b_noalloc_scratch_limit"])
+                                 "c2b_profile_enable", "c2b_profile_report", "c2b_noalloc_scratch_limit",
+                                 "c2b_device_malloc", "c2b_device_free", "c2b_copy_to_device", "c2b_copy_to_host",
+                                 "c2b_stream_synchronize"])
 
 
 class C2BError(RuntimeError):

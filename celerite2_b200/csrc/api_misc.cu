@@ -349,6 +349,32 @@ int c2b_add_inplace(int64_t n, const double *x, double *y, void *stream_) {
   return C2B_OK;
 }
 
+void *c2b_device_malloc(size_t bytes) {
+  void *p = nullptr;
+  if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) {
+    c2b::set_error("c2b_device_malloc: cudaMalloc of %zu bytes failed: %s", bytes, cudaGetErrorString(cudaGetLastError()));
+    return nullptr;
+  }
+  return p;
+}
+void c2b_device_free(void *ptr) {
+  if (ptr) cudaFree(ptr);
+}
+int c2b_copy_to_device(void *dst_device, const void *src_host, size_t bytes) {
+  if (bytes == 0) return C2B_OK;
+  C2B_CUDA(cudaMemcpy(dst_device, src_host, bytes, cudaMemcpyHostToDevice));
+  return C2B_OK;
+}
+int c2b_copy_to_host(void *dst_host, const void *src_device, size_t bytes) {
+  if (bytes == 0) return C2B_OK;
+  C2B_CUDA(cudaMemcpy(dst_host, src_device, bytes, cudaMemcpyDeviceToHost));
+  return C2B_OK;
+}
+int c2b_stream_synchronize(void *stream) {
+  C2B_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return C2B_OK;
+}
+
 int c2b_general_matmul_lower(int64_t N, int64_t M, int32_t J, int32_t K, const double *t1, const double *t2, const double *c,
                              const double *U, const double *V, const double *Y, double *Z, double *F, void *scratch,
                              size_t scratch_bytes, void *stream) {

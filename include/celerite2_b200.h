@@ -226,6 +226,18 @@ int c2b_solve_lower_noalloc(int64_t N, int32_t J, int32_t K, int64_t batch, cons
  */
 int c2b_add_inplace(int64_t n, const double *x, double *y, void *stream);
 
+/*
+ * Host-staging helpers for callers that hold HOST data and do not want to include CUDA headers (the drop-in C++
+ * header include/celerite2_b200/core.hpp uses them; the reference's callers pass host Eigen objects,
+ * c++/include/celerite2/forward.hpp).  Thin wrappers over cudaMalloc / cudaFree / cudaMemcpy / cudaStreamSynchronize
+ * on the current device.
+ */
+void *c2b_device_malloc(size_t bytes);
+void c2b_device_free(void *ptr);
+int c2b_copy_to_device(void *dst_device, const void *src_host, size_t bytes);
+int c2b_copy_to_host(void *dst_host, const void *src_device, size_t bytes);
+int c2b_stream_synchronize(void *stream);
+
 #ifdef __cplusplus
 }
 #endif
