@@ -146,6 +146,10 @@ C2B_DEV void cp_async8(double *smem_dst, const double *gmem_src) {
   const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem_src) : "memory");
 }
+C2B_DEV void cp_async16(double *smem_dst, const double *gmem_src) {  // both 16-byte aligned
+  const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
+}
 C2B_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 C2B_DEV void cp_async_wait() {

@@ -77,4 +77,56 @@ C2B_DEV void gload_matrix_row(double *gbuf, const double *grow, double *col, int
   __syncwarp();
 }
 
+// ---- per-group ring of input rows ------------------------------------------------------------------------------
+// The lane-group kernels walk a chunk row by row; a row's inputs (a few J-vectors, a few scalars, for factor_rev
+// also the J x J workspace row) must be in flight several rows ahead or every row pays the DRAM latency (r01d
+// profile: 45-48 % of the stall samples are long-scoreboard with one row of look-ahead).  The lanes of a group
+// copy row i+DEPTH into stage (i mod DEPTH) of a shared-memory ring with cp.async (no registers held) while row i
+// is consumed; every lane then reads whole J-vectors of the row from shared memory (broadcast within the group),
+// which also replaces the shuffle all-gathers of the inputs.
+// Use: prologue issue(0..DEPTH-1) each followed by commit(); per trip: acquire(); read; release(); issue(i+DEPTH);
+// commit().  All 32 lanes run every call (warp barriers inside acquire/release).
+template <int G, int ROWD, int DEPTH>
+struct GRing {
+  static_assert((DEPTH & (DEPTH - 1)) == 0, "DEPTH must be a power of two");
+  static_assert(ROWD % 2 == 0, "stages must stay 16-byte aligned");
+  double *base;  // shared memory of my group: DEPTH * ROWD doubles, 16-byte aligned
+  int c;         // my lane within the group
+  C2B_DEV double *stage(int i) const { return base + (i & (DEPTH - 1)) * ROWD; }
+  // cnt doubles at src -> offset off of stage i, the lanes of the group striding over them
+  C2B_DEV void copy(int i, int off, const double *src, int cnt) const {
+    double *dst = stage(i) + off;
+    for (int e = c; e < cnt; e += G) cp_async8(dst + e, src + e);
+  }
+  // same with 16-byte copies (src, off and cnt even / 16-byte aligned)
+  C2B_DEV void copy16(int i, int off, const double *src, int cnt) const {
+    double *dst = stage(i) + off;
+    for (int e = 2 * c; e < cnt; e += 2 * G) cp_async16(dst + e, src + e);
+  }
+  C2B_DEV void copy1(int i, int off, const double *src) const { cp_async8(stage(i) + off, src); }
+  C2B_DEV void commit() const { cp_async_commit(); }
+  C2B_DEV void acquire() const {
+    cp_async_wait<DEPTH - 1>();
+    __syncwarp();
+  }
+  C2B_DEV void release() const { __syncwarp(); }
+};
+
+// J consecutive doubles from 16-byte aligned shared memory
+template <int J>
+C2B_DEV void lds_row(const double *p, double *out) {
+  if constexpr (J % 2 == 0) {
+    const double2 *q = reinterpret_cast<const double2 *>(p);
+#pragma unroll
+    for (int j = 0; j < J / 2; ++j) {
+      const double2 v = q[j];
+      out[2 * j]      = v.x;
+      out[2 * j + 1]  = v.y;
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < J; ++j) out[j] = p[j];
+  }
+}
+
 }  // namespace c2b
