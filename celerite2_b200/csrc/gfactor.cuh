@@ -6,7 +6,7 @@
 
 namespace c2b {
 
-constexpr int kGroupThreads = 128;  // threads per CTA of the lane-group kernels
+constexpr int kGroupThreads = 64;   // threads per CTA of the lane-group kernels
 
 template <int J>
 __global__ void __launch_bounds__(kGroupThreads) gfactor_apply_kernel(FactorArgs g) {

@@ -8,7 +8,7 @@
 
 namespace c2b {
 
-constexpr int kGroupThreadsR = 128;
+constexpr int kGroupThreadsR = 64;
 
 // WRITE: produce the outputs (apply); otherwise only carry G (and the J rows of the congruence matrix M, lane k
 // holding row k) through the chunk (summary).  The summary never needs the workspace S: S enters only bU and the
@@ -22,7 +22,7 @@ __global__ void __launch_bounds__(kGroupThreadsR) gfactor_rev_kernel(FactorRevAr
   constexpr int ROWD  = (oX + 4 + 1) & ~1;
   constexpr int DEPTH = (J <= 8) ? 4 : 2;
   constexpr int JE    = (J + 1) & ~1;
-  __shared__ __align__(16) double sring[GP * DEPTH * ROWD];
+  __shared__ __align__(16) double sring[GP * GRing<G, ROWD, DEPTH>::kStride];
   __shared__ __align__(16) double sxch[GP * 2 * JE];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(kGroupThreadsR) gfactor_rev_kernel(FactorRevAr
   const double *d = g.d + b * g.N, *bd = g.bd + b * g.N;
   double *bt = WRITE ? g.bt + b * g.N : nullptr, *ba = WRITE ? g.ba + b * g.N : nullptr;
   double *bU = WRITE ? g.bU + b * NJ : nullptr, *bV = WRITE ? g.bV + b * NJ : nullptr;
-  GRing<G, ROWD, DEPTH> ring{sring + gin * DEPTH * ROWD, c};
+  GRing<G, ROWD, DEPTH> ring{sring + gin * GRing<G, ROWD, DEPTH>::kStride, c};
   double *xch         = sxch + gin * 2 * JE;
   const bool s16      = WRITE && (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
   const double cc     = act ? (g.c + b * g.c_bs)[c] : 0.0;

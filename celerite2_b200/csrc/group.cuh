@@ -90,7 +90,12 @@ template <int G, int ROWD, int DEPTH>
 struct GRing {
   static_assert((DEPTH & (DEPTH - 1)) == 0, "DEPTH must be a power of two");
   static_assert(ROWD % 2 == 0, "stages must stay 16-byte aligned");
-  double *base;  // shared memory of my group: DEPTH * ROWD doubles, 16-byte aligned
+  // Doubles between the rings of neighbouring groups.  The groups of a warp access the same offsets of their rings
+  // in one instruction; a stride that is a multiple of 128 bytes puts them all on the same banks (r01e profile:
+  // twice the ideal shared-memory wavefronts, L1 data pipe 68 % busy), so the stride is padded to G doubles
+  // modulo 16: the 32/G groups of a warp then tile the 32 banks.
+  static constexpr int kStride = DEPTH * ROWD + ((G % 16) - (DEPTH * ROWD) % 16 + 16) % 16;
+  double *base;  // shared memory of my group: kStride doubles, 16-byte aligned
   int c;         // my lane within the group
   C2B_DEV double *stage(int i) const { return base + (i & (DEPTH - 1)) * ROWD; }
   // cnt doubles at src -> offset off of stage i, the lanes of the group striding over them
@@ -109,7 +114,50 @@ struct GRing {
     cp_async_wait<DEPTH - 1>();
     __syncwarp();
   }
+  // rows i and i+1 are readable (one row less of look-ahead): lets a kernel evaluate the state-independent part of
+  // row i+1 (the exp) in the shadow of row i's dependent chain
+  C2B_DEV void acquire2() const {
+    cp_async_wait<DEPTH - 2>();
+    __syncwarp();
+  }
   C2B_DEV void release() const { __syncwarp(); }
+};
+
+// One lane's share of the scalar inputs of a row (t_n, y_n, ...): scalar e of the row is copied by lane G-1-e (the
+// lanes that own no column first), scalars e >= G wrap around.  Everything that depends only on the lane is
+// resolved before the loop, so a row costs one clamp and one copy per scalar.
+template <int G, int NS>
+struct ScalarStreams {
+  static constexpr int NSL = (NS + G - 1) / G;
+  const double *base[NSL];
+  int64_t del[NSL];
+  bool on[NSL];
+  // src[e] = array of scalar e, delta[e] = row offset (0, or -1/+1 for the neighbouring time stamp, clamped to [0, N-1])
+  C2B_DEV void init(int c, bool has, const double *const *src, const int *delta) {
+#pragma unroll
+    for (int k = 0; k < NSL; ++k) {
+      const int e = G - 1 - c + k * G;
+      on[k]       = has && e < NS;
+      base[k]     = src[0];
+      del[k]      = 0;
+#pragma unroll
+      for (int x = 0; x < NS; ++x)
+        if (e == x) {
+          base[k] = src[x];
+          del[k]  = delta[x];
+        }
+    }
+  }
+  template <class Ring>
+  C2B_DEV void issue(const Ring &ring, int i, int off, int c, int64_t n, int64_t N) const {
+#pragma unroll
+    for (int k = 0; k < NSL; ++k)
+      if (on[k]) {
+        int64_t idx = n + del[k];
+        idx         = idx < 0 ? 0 : (idx > N - 1 ? N - 1 : idx);
+        ring.copy1(i, off + (G - 1 - c + k * G), base[k] + idx);
+      }
+  }
 };
 
 // J consecutive doubles from 16-byte aligned shared memory
