@@ -160,6 +160,46 @@ struct ScalarStreams {
   }
 };
 
+// ---- per-group tiles of input rows -------------------------------------------------------------------------------
+// Second generation of the input staging (r01e profile: with one row per trip the loop is one long serial
+// instruction stream of ~150 instructions at ~6 cycles each; a third of it is the per-row copy bookkeeping and
+// another third the exp, which does not depend on the state).  A group now stages TILES of R consecutive rows:
+// the rows of a tile are contiguous in global memory, so a field of the tile is one run of R*J doubles that the
+// lanes copy with 16-byte cp.async; the kernel's row loop is fully unrolled over the tile, which gives constant
+// shared-memory offsets, one wait + barrier per tile instead of per row, and lets the compiler interleave the R
+// independent exp evaluations of the tile.  Two tile buffers per group: tile k+1 lands while tile k is consumed.
+//
+// Buffer slots: slot s of a tile holds global row lo + s - pad, where pad = 0 for kernels walking upwards and
+// R - rows for kernels walking downwards (a short last tile is aligned to the END of the buffer), so that step r of
+// the unrolled loop always reads slot r (upwards) or R-1-r (downwards).
+template <int G>
+struct GCopy {
+  int c;  // my lane within the group
+  // cnt contiguous doubles; wide: cnt even, src and dst 16-byte aligned
+  C2B_DEV void run(double *dst, const double *src, int cnt, bool wide) const {
+    if (wide) {
+      for (int e = 2 * c; e < cnt; e += 2 * G) cp_async16(dst + e, src + e);
+    } else {
+      for (int e = c; e < cnt; e += G) cp_async8(dst + e, src + e);
+    }
+  }
+  // time stamps with one neighbour on either side: dst[e] = t[clamp(first + e, 0, N-1)], e < cnt.  The clamp makes
+  // dt = 0 (propagator exactly 1) at the two ends of the series, which is what the recursions want there.
+  C2B_DEV void run_t(double *dst, const double *t, int64_t first, int cnt, int64_t N) const {
+    for (int e = c; e < cnt; e += G) {
+      int64_t i = first + e;
+      i         = i < 0 ? 0 : (i > N - 1 ? N - 1 : i);
+      cp_async8(dst + e, t + i);
+    }
+  }
+};
+
+// doubles per group for NBUF tile buffers of TB doubles each, padded like GRing::kStride
+template <int G, int TB, int NBUF>
+struct GTileStride {
+  static constexpr int value = NBUF * TB + ((G % 16) - (NBUF * TB) % 16 + 16) % 16;
+};
+
 // J consecutive doubles from 16-byte aligned shared memory
 template <int J>
 C2B_DEV void lds_row(const double *p, double *out) {

@@ -9,17 +9,20 @@ namespace c2b {
 
 constexpr int kGroupThreadsS = 64;
 
-constexpr int kSweepDepth = 8;  // rows of look-ahead in the per-group input ring (group.cuh)
+constexpr int kTileRows = 8;  // rows per staged tile (group.cuh)
 
 // ---- forward apply -----------------------------------------------------------------------------------------------
-// ring row: A[J] B[J] | y, t_n, t_other, z_old
+// tile buffer: A[R*J] B[R*J] | t[R+2] y[R] z_old[R]
 template <int J, bool SOLVE, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS) gsweep_apply_kernel(SweepArgs a) {
-  constexpr int G    = GroupOf<J>::G;
-  constexpr int GP   = kGroupThreadsS / G;
-  constexpr int oX   = 2 * J;
-  constexpr int ROWD = (oX + 4 + 1) & ~1;
-  __shared__ __align__(16) double sring[GP * GRing<G, ROWD, kSweepDepth>::kStride];
+  constexpr int G   = GroupOf<J>::G;
+  constexpr int GP  = kGroupThreadsS / G;
+  constexpr int R   = kTileRows;
+  constexpr int oB  = R * J, oT = 2 * R * J, oY = oT + R + 2, oZ = oY + R;
+  constexpr int TB  = (oZ + (SOLVE ? 0 : R) + 1) & ~1;
+  constexpr int GS  = GTileStride<G, TB, 2>::value;
+  constexpr int dir = LOWER ? 1 : -1;
+  __shared__ __align__(16) double stile[GP * GS];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -32,87 +35,91 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_apply_kernel(SweepArgs 
   const double *t     = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
   double *Z = a.Z + b * a.N, *F = a.F ? a.F + b * a.N * J : nullptr;
-  GRing<G, ROWD, kSweepDepth> ring{sring + gin * GRing<G, ROWD, kSweepDepth>::kStride, c};
+  double *gbuf = stile + gin * GS;
+  const GCopy<G> cp{c};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
   double Fc = 0.0;
   if (a.carry && act) {
     const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
     Fc                 = a.carry[(b * a.node_stride + leaf) * (int64_t)J + c];
   }
-  const int cnt   = (int)(n1 - n0);
-  const int trips = warp_max(cnt);
-  // rows are visited in the order nf, nf + dir, ...
-  constexpr int dir = LOWER ? 1 : -1;
-  const int64_t nf  = LOWER ? n0 : n1 - 1;
-  const double *pA = A + nf * J + cj, *pB = B + nf * J + cj;
-  double *pF = F ? F + nf * J + cj : nullptr, *pZ = Z + nf;
-  constexpr int NS = SOLVE ? 3 : 4;
-  ScalarStreams<G, NS> sc;
-  {
-    const double *src[4] = {Y, t, t, Z};
-    const int delta[4]   = {0, 0, -dir, 0};
-    sc.init(c, has, src, delta);
-  }
-  auto issue = [&](int i) {
-    if (i < cnt) {
-      if (c < J) {
-        ring.copy1(i, c, pA + (int64_t)(dir * J) * i);
-        ring.copy1(i, J + c, pB + (int64_t)(dir * J) * i);
-      }
-      sc.issue(ring, i, oX, c, nf + dir * i, a.N);
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  // tile k (processing order) = rows [lo, lo + rows)
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = LOWER ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
+      const int pad    = LOWER ? 0 : R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run(tb + oY + pad, Y + lo, rows, false);
+      if (!SOLVE) cp.run(tb + oZ + pad, Z + lo, rows, false);
     }
-    ring.commit();
+    cp_async_commit();
   };
+  issue(0);
+  issue(1);
+  const int64_t nf = LOWER ? n0 : n1 - 1;  // first row visited
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    // state-independent part of the whole tile first: R independent exp evaluations the compiler can interleave
+    double p[R];
 #pragma unroll
-  for (int s = 0; s < kSweepDepth; ++s) issue(s);
-  const int64_t nedge = LOWER ? 0 : a.N - 1;
-  // exp(c dt) of row i does not depend on the state: it is evaluated one trip ahead
-  auto prop = [&](int i) {
-    const double *rb = ring.stage(i);
-    const double dt  = LOWER ? rb[oX + 2] - rb[oX + 1] : rb[oX + 1] - rb[oX + 2];
-    return (i >= cnt || nf + dir * i == nedge) ? 1.0 : exp(cc * dt);
-  };
-  ring.acquire2();
-  double p_next = prop(0);
-  for (int i = 0; i < trips; ++i) {
-    const bool live = i < cnt;
-    ring.acquire2();
-    const double *rb  = ring.stage(i);
-    const double a_c  = (live && act) ? rb[cj] : 0.0;
-    const double b_c  = (live && act) ? rb[J + cj] : 0.0;
-    const double y    = rb[oX];
-    const double zold = SOLVE ? 0.0 : rb[oX + 3];
-    const double p_c  = p_next;
-    p_next            = prop(i + 1);
-    ring.release();
-    issue(i + kSweepDepth);
-    if (pF && live && act) pF[(int64_t)(dir * J) * i] = Fc;
-    Fc             = p_c * Fc;
-    const double s = gsum<G>(a_c * Fc);
-    double z, r;
-    if (SOLVE) {
-      z = y - s;
-      r = z;
-    } else {
-      z = zold + s;
-      r = y;
+    for (int r = 0; r < R; ++r) {
+      const int s     = LOWER ? r : R - 1 - r;
+      const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+      p[r]            = exp(cc * dt);
     }
-    if (live && c == G - 1) pZ[(int64_t)dir * i] = z;
-    Fc = fma(b_c, r, Fc);
+    double *Ft = F ? F + (nf + (int64_t)dir * k * R) * J + cj : nullptr;
+    double *Zt = Z + (nf + (int64_t)dir * k * R);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s       = LOWER ? r : R - 1 - r;
+      const bool live   = r < rows;
+      const double a_c  = (live && act) ? tb[s * J + cj] : 0.0;
+      const double b_c  = (live && act) ? tb[oB + s * J + cj] : 0.0;
+      const double y    = tb[oY + s];
+      const double zold = SOLVE ? 0.0 : tb[oZ + s];
+      if (Ft && live && act) Ft[dir * J * r] = Fc;
+      Fc             = p[r] * Fc;
+      const double sm = gsum<G>(a_c * Fc);
+      double z, rr;
+      if (SOLVE) {
+        z  = y - sm;
+        rr = z;
+      } else {
+        z  = zold + sm;
+        rr = y;
+      }
+      if (live && c == G - 1) Zt[dir * r] = z;
+      Fc = fma(b_c, rr, Fc);
+    }
+    __syncwarp();
+    issue(k + 2);
   }
 }
 
 // ---- forward summary, solves: lane q carries column q ----------------------------------------------------------------
-// ring row: A[J] B[J] | y, t_n, t_other
+// tile buffer: A[R*J] B[R*J] | t[R+2] y[R]; plus one R x J block per group for the propagators of the tile
 template <int J, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS) gsweep_summary_kernel(SweepArgs a) {
-  constexpr int G    = GroupOf<J + 1>::G;  // J + 1 columns
-  constexpr int GP   = kGroupThreadsS / G;
-  constexpr int oX   = 2 * J;
-  constexpr int ROWD = (oX + 3 + 1) & ~1;
-  constexpr int JE   = (J + 1) & ~1;
-  __shared__ __align__(16) double sring[GP * GRing<G, ROWD, kSweepDepth>::kStride];
-  __shared__ __align__(16) double sxch[GP * JE];
+  constexpr int G  = GroupOf<J + 1>::G;  // J + 1 columns
+  constexpr int GP = kGroupThreadsS / G;
+  constexpr int R  = kTileRows;
+  constexpr int JE = (J + 1) & ~1;
+  constexpr int oB = R * J, oT = 2 * R * J, oY = oT + R + 2;
+  constexpr int TB = (oY + R + 1) & ~1;
+  constexpr int GS = GTileStride<G, TB, 2>::value;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ __align__(16) double sprop[GP * R * JE];
   const int q         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -123,59 +130,67 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_summary_kernel(SweepArg
   const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
   const double *t     = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
-  GRing<G, ROWD, kSweepDepth> ring{sring + gin * GRing<G, ROWD, kSweepDepth>::kStride, q};
-  double *xch     = sxch + gin * JE;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE;
+  const GCopy<G> cp{q};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
   double Gq[J];
 #pragma unroll
   for (int j = 0; j < J; ++j) Gq[j] = (j == q) ? 1.0 : 0.0;
-  const int cnt   = (int)(n1 - n0);
-  const int trips = warp_max(cnt);
-  auto row = [&](int i) { return LOWER ? n0 + i : n1 - 1 - i; };
-  auto issue = [&](int i) {
-    if (i < cnt) {
-      const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
-      if (q < J) {
-        ring.copy1(i, q, A + n * J + q);
-        ring.copy1(i, J + q, B + n * J + q);
-      }
-      for (int e = G - 1 - q; e < 3; e += G) {
-        const double *src = e == 0 ? Y + n : (e == 1 ? t + n : t + ((o >= 0 && o < a.N) ? o : n));
-        ring.copy1(i, oX + e, src);
-      }
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = LOWER ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
+      const int pad    = LOWER ? 0 : R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run(tb + oY + pad, Y + lo, rows, false);
     }
-    ring.commit();
+    cp_async_commit();
   };
+  issue(0);
+  issue(1);
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    if (q < J) {
 #pragma unroll
-  for (int s = 0; s < kSweepDepth; ++s) issue(s);
-  for (int i = 0; i < trips; ++i) {
-    const bool live = i < cnt;
-    const int64_t n = live ? row(i) : 0;
-    ring.acquire();
-    const double *rb = ring.stage(i);
-    double av[J], bv[J];
-    lds_row<J>(rb, av);
-    lds_row<J>(rb + J, bv);
-    const double y     = rb[oX];
-    const double t_cur = rb[oX + 1], t_oth = rb[oX + 2];
-    const bool edge    = LOWER ? (n == 0) : (n == a.N - 1);
-    const double dt    = LOWER ? t_oth - t_cur : t_cur - t_oth;
-    if (act) xch[q] = (edge || !live) ? 1.0 : exp(cc * dt);
-    ring.release();  // also publishes xch
-    issue(i + kSweepDepth);
-    double p[J];
-    lds_row<J>(xch, p);
-    if (live) {
-      double s = 0.0;
-#pragma unroll
-      for (int j = 0; j < J; ++j) {
-        Gq[j] = p[j] * Gq[j];
-        s     = fma(av[j], Gq[j], s);
+      for (int r = 0; r < R; ++r) {
+        const int s     = LOWER ? r : R - 1 - r;
+        const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+        pb[r * JE + q]  = exp(cc * dt);
       }
-      const double r = (q == J ? y : 0.0) - s;
-#pragma unroll
-      for (int j = 0; j < J; ++j) Gq[j] = fma(bv[j], r, Gq[j]);
     }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s = LOWER ? r : R - 1 - r;
+      double av[J], bv[J], p[J];
+      lds_row<J>(tb + s * J, av);
+      lds_row<J>(tb + oB + s * J, bv);
+      lds_row<J>(pb + r * JE, p);
+      const double y = tb[oY + s];
+      if (r < rows) {
+        double sm = 0.0;
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+          Gq[j] = p[j] * Gq[j];
+          sm    = fma(av[j], Gq[j], sm);
+        }
+        const double rr = (q == J ? y : 0.0) - sm;
+#pragma unroll
+        for (int j = 0; j < J; ++j) Gq[j] = fma(bv[j], rr, Gq[j]);
+      }
+    }
+    __syncwarp();
+    issue(k + 2);
   }
   if (has && q <= J) {
     const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
@@ -191,14 +206,18 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_summary_kernel(SweepArg
 }
 
 // ---- reverse apply -----------------------------------------------------------------------------------------------------
-// ring row: A[J] B[J] F[J] | bZ, Z or Y, t_n, t_other
+// tile buffer: A[R*J] B[R*J] F[R*J] | t[R+2] bZ[R] (Z or Y)[R]
 template <int J, bool SOLVE, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_apply_kernel(SweepRevArgs a) {
-  constexpr int G    = GroupOf<J>::G;
-  constexpr int GP   = kGroupThreadsS / G;
-  constexpr int oX   = 3 * J;
-  constexpr int ROWD = (oX + 4 + 1) & ~1;
-  __shared__ __align__(16) double sring[GP * GRing<G, ROWD, kSweepDepth>::kStride];
+  constexpr int G   = GroupOf<J>::G;
+  constexpr int GP  = kGroupThreadsS / G;
+  constexpr int R   = kTileRows;
+  constexpr int oB  = R * J, oF = 2 * R * J, oT = 3 * R * J, oZ = oT + R + 2, oY = oZ + R;
+  constexpr int TB  = (oY + R + 1) & ~1;
+  constexpr int GS  = GTileStride<G, TB, 2>::value;
+  constexpr bool UP = !LOWER;  // the reverse of a lower sweep walks downwards
+  constexpr int dir = UP ? 1 : -1;
+  __shared__ __align__(16) double stile[GP * GS];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -213,7 +232,9 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_apply_kernel(SweepR
   const double *A = a.A + b * NJ, *B = a.B + b * NJ, *F = a.F + b * NJ, *bZ = a.bZ + b * a.N;
   const double *ZY = SOLVE ? a.Z + b * a.N : a.Y + b * a.y_bs;
   double *bt = a.bt + b * a.N, *bA = a.bA + b * NJ, *bB = a.bB + b * NJ, *bY = a.bY + b * a.N;
-  GRing<G, ROWD, kSweepDepth> ring{sring + gin * GRing<G, ROWD, kSweepDepth>::kStride, c};
+  double *gbuf = stile + gin * GS;
+  const GCopy<G> cp{c};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(F)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
   double bF = 0.0, bc_acc = 0.0, pend = 0.0;
   if (a.carry && act) {
@@ -222,83 +243,100 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_apply_kernel(SweepR
   }
   const double sgn = LOWER ? 1.0 : -1.0;
   const int cnt    = (int)(n1 - n0);
-  const int trips  = warp_max(cnt);
-  auto row = [&](int i) { return LOWER ? n1 - 1 - i : n0 + i; };
-  auto issue = [&](int i) {
-    if (i < cnt) {
-      const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
-      if (c < J) {
-        ring.copy1(i, c, A + n * J + c);
-        ring.copy1(i, J + c, B + n * J + c);
-        ring.copy1(i, 2 * J + c, F + n * J + c);
-      }
-      for (int e = G - 1 - c; e < 4; e += G) {
-        const double *src = e == 0 ? bZ + n : (e == 1 ? ZY + n : (e == 2 ? t + n : t + ((o >= 0 && o < a.N) ? o : n)));
-        ring.copy1(i, oX + e, src);
-      }
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = UP ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
+      const int pad    = UP ? 0 : R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
+      cp.run(tb + oF + pad * J, F + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run(tb + oZ + pad, bZ + lo, rows, false);
+      cp.run(tb + oY + pad, ZY + lo, rows, false);
     }
-    ring.commit();
+    cp_async_commit();
   };
+  issue(0);
+  issue(1);
+  const int64_t nf    = UP ? n0 : n1 - 1;  // first row visited
+  const int64_t nlast = LOWER ? 0 : a.N - 1;  // the row without a predecessor in this direction
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    double p[R], dts[R];
 #pragma unroll
-  for (int s = 0; s < kSweepDepth; ++s) issue(s);
-  for (int i = 0; i < trips; ++i) {
-    const bool live = i < cnt;
-    const int64_t n = live ? row(i) : 0;
-    const int64_t o = LOWER ? n - 1 : n + 1;
-    const bool nb   = live && o >= 0 && o < a.N;
-    ring.acquire();
-    const double *rb   = ring.stage(i);
-    const double a_c   = (live && act) ? rb[cj] : 0.0;
-    const double b_c   = (live && act) ? rb[J + cj] : 0.0;
-    const double Fn    = (nb && act) ? rb[2 * J + cj] : 0.0;
-    const double bz0   = rb[oX], zy = rb[oX + 1];
-    const double t_cur = rb[oX + 2], t_oth = rb[oX + 3];
-    ring.release();
-    issue(i + kSweepDepth);
-    const double dot = gsum<G>(b_c * bF);
-    double bz;
-    if (SOLVE) {
-      bz = bz0 + dot;
-      if (live && c == G - 1) bY[n] = bz;
-    } else {
-      bz = bz0;
-      if (live && c == G - 1) bY[n] = dot;
+    for (int r = 0; r < R; ++r) {
+      const int s = UP ? r : R - 1 - r;
+      dts[r]      = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+      p[r]        = exp(cc * dts[r]);
     }
-    if (live && act) bB[n * J + c] = zy * bF;
-    const double dt  = sgn * (t_oth - t_cur);
-    const double p_c = nb ? exp(cc * dt) : 1.0;
-    const double au  = a_c * bz;
-    const double nf  = SOLVE ? bF - au : bF + au;
-    const double pf  = p_c * Fn;
-    const double bp  = nb ? Fn * nf * p_c : 0.0;
-    const double fac = gsum<G>(cc * bp);
-    if (nb) {
-      if (act) bA[n * J + c] = SOLVE ? -(bz * pf) : bz * pf;
-      bc_acc = fma(dt, bp, bc_acc);
-      if (c == 0) bt[n] = pend - sgn * fac;
-      pend = sgn * fac;
-      bF   = p_c * nf;
-    } else if (live) {
-      if (act) bA[n * J + c] = 0.0;
-      if (c == 0) bt[n] = pend;
-      pend = 0.0;
+    const int64_t nt = nf + (int64_t)dir * k * R;  // first row of this tile in visiting order
+    double *bAt = bA + nt * J + cj, *bBt = bB + nt * J + cj, *btt = bt + nt, *bYt = bY + nt;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s      = UP ? r : R - 1 - r;
+      const bool live  = r < rows;
+      const bool nb    = live && (nt + dir * r != nlast);
+      const double a_c = (live && act) ? tb[s * J + cj] : 0.0;
+      const double b_c = (live && act) ? tb[oB + s * J + cj] : 0.0;
+      const double Fn  = (nb && act) ? tb[oF + s * J + cj] : 0.0;
+      const double bz0 = tb[oZ + s], zy = tb[oY + s];
+      const double dot = gsum<G>(b_c * bF);
+      double bz;
+      if (SOLVE) {
+        bz = bz0 + dot;
+        if (live && c == G - 1) bYt[dir * r] = bz;
+      } else {
+        bz = bz0;
+        if (live && c == G - 1) bYt[dir * r] = dot;
+      }
+      if (live && act) bBt[dir * J * r] = zy * bF;
+      const double p_c = p[r];
+      const double au  = a_c * bz;
+      const double nf_ = SOLVE ? bF - au : bF + au;
+      const double pf  = p_c * Fn;
+      const double bp  = nb ? Fn * nf_ * p_c : 0.0;
+      const double fac = gsum<G>(cc * bp);
+      if (nb) {
+        if (act) bAt[dir * J * r] = SOLVE ? -(bz * pf) : bz * pf;
+        bc_acc = fma(dts[r], bp, bc_acc);
+        if (c == 0) btt[dir * r] = pend - sgn * fac;
+        pend = sgn * fac;
+        bF   = p_c * nf_;
+      } else if (live) {
+        if (act) bAt[dir * J * r] = 0.0;
+        if (c == 0) btt[dir * r] = pend;
+        pend = 0.0;
+      }
     }
+    __syncwarp();
+    issue(k + 2);
   }
   if (act) a.bc_part[(b * a.C + chunk) * J + c] = bc_acc;
   if (has && c == 0) a.bt_edge[b * a.C + chunk] = pend;
 }
 
 // ---- reverse summary, solves -----------------------------------------------------------------------------------------
-// ring row: A[J] B[J] | bZ, t_n, t_other
+// tile buffer: A[R*J] B[R*J] | t[R+2] bZ[R]; plus the R x J propagator block
 template <int J, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_summary_kernel(SweepRevArgs a) {
-  constexpr int G    = GroupOf<J + 1>::G;
-  constexpr int GP   = kGroupThreadsS / G;
-  constexpr int oX   = 2 * J;
-  constexpr int ROWD = (oX + 3 + 1) & ~1;
-  constexpr int JE   = (J + 1) & ~1;
-  __shared__ __align__(16) double sring[GP * GRing<G, ROWD, kSweepDepth>::kStride];
-  __shared__ __align__(16) double sxch[GP * JE];
+  constexpr int G   = GroupOf<J + 1>::G;
+  constexpr int GP  = kGroupThreadsS / G;
+  constexpr int R   = kTileRows;
+  constexpr int JE  = (J + 1) & ~1;
+  constexpr int oB  = R * J, oT = 2 * R * J, oZ = oT + R + 2;
+  constexpr int TB  = (oZ + R + 1) & ~1;
+  constexpr int GS  = GTileStride<G, TB, 2>::value;
+  constexpr bool UP = !LOWER;
+  constexpr int dir = UP ? 1 : -1;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ __align__(16) double sprop[GP * R * JE];
   const int q         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -309,56 +347,66 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_summary_kernel(Swee
   const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
   const double *t     = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *bZ = a.bZ + b * a.N;
-  GRing<G, ROWD, kSweepDepth> ring{sring + gin * GRing<G, ROWD, kSweepDepth>::kStride, q};
-  double *xch     = sxch + gin * JE;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE;
+  const GCopy<G> cp{q};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
   double Gq[J];
 #pragma unroll
   for (int j = 0; j < J; ++j) Gq[j] = (j == q) ? 1.0 : 0.0;
-  const double sgn = LOWER ? 1.0 : -1.0;
   const int cnt    = (int)(n1 - n0);
-  const int trips  = warp_max(cnt);
-  auto row = [&](int i) { return LOWER ? n1 - 1 - i : n0 + i; };
-  auto issue = [&](int i) {
-    if (i < cnt) {
-      const int64_t n = row(i), o = LOWER ? n - 1 : n + 1;
-      if (q < J) {
-        ring.copy1(i, q, A + n * J + q);
-        ring.copy1(i, J + q, B + n * J + q);
-      }
-      for (int e = G - 1 - q; e < 3; e += G) {
-        const double *src = e == 0 ? bZ + n : (e == 1 ? t + n : t + ((o >= 0 && o < a.N) ? o : n));
-        ring.copy1(i, oX + e, src);
-      }
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = UP ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
+      const int pad    = UP ? 0 : R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run(tb + oZ + pad, bZ + lo, rows, false);
     }
-    ring.commit();
+    cp_async_commit();
   };
+  issue(0);
+  issue(1);
+  const int64_t nf    = UP ? n0 : n1 - 1;
+  const int64_t nlast = LOWER ? 0 : a.N - 1;
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    if (q < J) {
 #pragma unroll
-  for (int s = 0; s < kSweepDepth; ++s) issue(s);
-  for (int i = 0; i < trips; ++i) {
-    const bool live = i < cnt;
-    const int64_t n = live ? row(i) : 0;
-    const int64_t o = LOWER ? n - 1 : n + 1;
-    const bool nb   = live && o >= 0 && o < a.N;
-    ring.acquire();
-    const double *rb = ring.stage(i);
-    double av[J], bv[J];
-    lds_row<J>(rb, av);
-    lds_row<J>(rb + J, bv);
-    const double bz0   = rb[oX];
-    const double t_cur = rb[oX + 1], t_oth = rb[oX + 2];
-    if (act) xch[q] = nb ? exp(cc * sgn * (t_oth - t_cur)) : 1.0;
-    ring.release();  // also publishes xch
-    issue(i + kSweepDepth);
-    double p[J];
-    lds_row<J>(xch, p);
-    if (nb) {
-      double bz = (q == J) ? bz0 : 0.0;
-#pragma unroll
-      for (int j = 0; j < J; ++j) bz = fma(bv[j], Gq[j], bz);
-#pragma unroll
-      for (int j = 0; j < J; ++j) Gq[j] = p[j] * fma(-av[j], bz, Gq[j]);
+      for (int r = 0; r < R; ++r) {
+        const int s     = UP ? r : R - 1 - r;
+        const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+        pb[r * JE + q]  = exp(cc * dt);
+      }
     }
+    __syncwarp();
+    const int64_t nt = nf + (int64_t)dir * k * R;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s = UP ? r : R - 1 - r;
+      double av[J], bv[J], p[J];
+      lds_row<J>(tb + s * J, av);
+      lds_row<J>(tb + oB + s * J, bv);
+      lds_row<J>(pb + r * JE, p);
+      const double bz0 = tb[oZ + s];
+      if (r < rows && nt + dir * r != nlast) {
+        double bz = (q == J) ? bz0 : 0.0;
+#pragma unroll
+        for (int j = 0; j < J; ++j) bz = fma(bv[j], Gq[j], bz);
+#pragma unroll
+        for (int j = 0; j < J; ++j) Gq[j] = p[j] * fma(-av[j], bz, Gq[j]);
+      }
+    }
+    __syncwarp();
+    issue(k + 2);
   }
   if (has && q <= J) {
     const int64_t leaf = LOWER ? a.C - 1 - chunk : chunk;
