@@ -8,16 +8,36 @@ namespace c2b {
 
 constexpr int kGroupThreads = 64;   // threads per CTA of the lane-group kernels
 
+// rows per staged tile (group.cuh); the apply pass collects SR workspace rows (SR*J*J doubles) in shared memory
+// before writing them out with wide stores (shared memory per CTA decides how many CTAs fit on an SM)
+template <int J>
+struct FactorTile {
+  static constexpr int R  = J <= 8 ? 8 : 2;
+  static constexpr int SR = J <= 8 ? 4 : 2;
+};
+
+// tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 template <int J>
 __global__ void __launch_bounds__(kGroupThreads) gfactor_apply_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;  // groups per CTA
-  __shared__ double srow[GP * J * J];
+  constexpr int R  = FactorTile<J>::R;
+  constexpr int JE = (J + 1) & ~1;
+  constexpr int oV = R * J, oT = 2 * R * J, oA = oT + R + 2;
+  constexpr int TB = (oA + R + 1) & ~1;
+  constexpr int GS = GTileStride<G, TB, 2>::value;
+  constexpr int SR = FactorTile<J>::SR;
+  constexpr int SS = GTileStride<G, SR * J * J, 1>::value;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ __align__(16) double sprop[GP * R * JE];
+  __shared__ __align__(16) double sxch[GP * 2 * JE];
+  __shared__ __align__(16) double srows[GP * SS];  // the tile's S rows, flushed with wide stores once per tile
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
   const int64_t unit   = (int64_t)blockIdx.x * GP + gin;
   const bool has       = unit < g.batch * g.C;
   const bool act       = has && c < J;
+  const int cj         = c < J ? c : 0;
   const int64_t chunk  = has ? unit % g.C : 0, b = has ? unit / g.C : 0;
   const int64_t n0     = chunk * g.L;
   const int64_t n1     = has ? (n0 + g.L < g.N ? n0 + g.L : g.N) : n0;
@@ -26,8 +46,11 @@ __global__ void __launch_bounds__(kGroupThreads) gfactor_apply_kernel(FactorArgs
   const double *a = g.a + b * g.N, *U = g.U + b * NJ, *V = g.V + b * NJ;
   double *d = g.d + b * g.N, *W = g.W + b * NJ;
   double *S = g.S ? g.S + b * NJ * J : nullptr;
-  double *gbuf       = srow + gin * J * J;
-  const double cc    = act ? (g.c + b * g.c_bs)[c] : 0.0;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 2 * JE, *sbuf = srows + gin * SS;
+  const GCopy<G> cp{c};
+  const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
+  const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
+  const double cc  = act ? (g.c + b * g.c_bs)[c] : 0.0;
   double Sg[J];  // column c of Sigma: Sg[j] = Sigma(j, c)
 #pragma unroll
   for (int j = 0; j < J; ++j) Sg[j] = 0.0;
@@ -36,74 +59,126 @@ __global__ void __launch_bounds__(kGroupThreads) gfactor_apply_kernel(FactorArgs
 #pragma unroll
     for (int j = 0; j < J; ++j) Sg[j] = -st[j * J + c];
   }
-  // software pipeline: the next row's inputs are loaded while the current row is computed
-  double tn = 0.0, tp = 0.0, an = 0.0, un = 0.0, vn = 0.0;
-  if (n0 < n1) {
-    tn = t[n0];
-    tp = n0 > 0 ? t[n0 - 1] : tn;
-    an = a[n0];
-    un = act ? U[n0 * J + c] : 0.0;
-    vn = act ? V[n0 * J + c] : 0.0;
-  }
-  bool alive       = has;
-  const int trips  = warp_max((int)(n1 - n0));
-  for (int i = 0; i < trips; ++i) {
-    const int64_t n = n0 + i;
-    if (n >= n1) alive = false;  // this group's chunk is done; keep the warp converged
-    const double t_cur = tn, t_prev = tp, a_cur = an, u_c = un, v_c = vn;
-    if (n + 1 < n1) {
-      tn = t[n + 1];
-      an = a[n + 1];
-      un = act ? U[(n + 1) * J + c] : 0.0;
-      vn = act ? V[(n + 1) * J + c] : 0.0;
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = n0 + (int64_t)k * R;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb, U + lo * J, rows * J, wide);
+      cp.run(tb + oV, V + lo * J, rows * J, wide);
+      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.N);
+      cp.run(tb + oA, a + lo, rows, false);
     }
-    tp = t_cur;
-    const double p_c = (n == 0) ? 1.0 : exp(cc * (t_prev - t_cur));
-    double p[J], u[J];
-    gall<G, J>(p_c, p);
-    gall<G, J>(u_c, u);
-    double St[J];
+    cp_async_commit();
+  };
+  issue(0);
+  issue(1);
+  bool alive = has;
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    const int64_t nt = n0 + (int64_t)k * R;
+    if (c < J) {
 #pragma unroll
-    for (int j = 0; j < J; ++j) {
-      St[j] = p[j] * Sg[j];
-      Sg[j] = St[j] * p_c;
+      for (int r = 0; r < R; ++r) pb[r * JE + c] = exp(cc * (tb[oT + r] - tb[oT + r + 1]));  // dt = 0 at n = 0
     }
-    if (S) gstore_matrix_row<G, J>(gbuf, S + n * (int64_t)J * J, St, c, act, alive);
-    double tmp = 0.0;
+    __syncwarp();
+    int stored = 0;  // S rows of this tile that are to be written
 #pragma unroll
-    for (int j = 0; j < J; ++j) tmp = fma(u[j], Sg[j], tmp);
-    const double dn = a_cur - gsum<G>(tmp * u_c);
-    if (alive && c == 0) d[n] = dn;
-    if (alive && n >= 1 && dn <= 0.0) {
-      if (c == 0) record_failure(g.status ? g.status + b : nullptr, n);
-      alive = false;  // forward.hpp:128: later rows stay untouched (lanes keep participating in the shuffles)
+    for (int r = 0; r < R; ++r) {
+      if (r >= rows) alive = false;  // this group's chunk is done; keep the warp converged
+      const int64_t n = nt + r;
+      double p[J], u[J];
+      lds_row<J>(pb + r * JE, p);
+      lds_row<J>(tb + r * J, u);
+      const double p_c = act ? pb[r * JE + cj] : 1.0;
+      const double u_c = act ? tb[r * J + cj] : 0.0;
+      const double v_c = act ? tb[oV + r * J + cj] : 0.0;
+      const double a_n = tb[oA + r];
+      double St[J];
+#pragma unroll
+      for (int j = 0; j < J; ++j) {
+        St[j] = p[j] * Sg[j];
+        Sg[j] = St[j] * p_c;
+      }
+      if (S && act) {
+#pragma unroll
+        for (int j = 0; j < J; ++j) sbuf[(r % SR) * J * J + J * c + j] = St[j];  // element (j, c) at j + J*c
+      }
+      if (alive) stored = r % SR + 1;
+      double tmp = 0.0;
+#pragma unroll
+      for (int j = 0; j < J; ++j) tmp = fma(u[j], Sg[j], tmp);
+      const double dn = a_n - gsum<G>(tmp * u_c);
+      if (alive && c == G - 1) d[n] = dn;
+      if (alive && n >= 1 && dn <= 0.0) {
+        if (c == 0) record_failure(g.status ? g.status + b : nullptr, n);
+        alive = false;  // forward.hpp:128: later rows stay untouched (lanes keep participating in the barriers)
+      }
+      const double w_c = (v_c - tmp) / dn;
+      if (alive && act) W[n * J + c] = w_c;
+      double *xw = xch + (r & 1) * JE;
+      if (c < J) xw[c] = w_c;
+      __syncwarp();
+      double w[J];
+      lds_row<J>(xw, w);
+      const double dw = dn * w_c;
+#pragma unroll
+      for (int j = 0; j < J; ++j) Sg[j] = fma(w[j], dw, Sg[j]);
+      if ((r + 1) % SR == 0) {
+        // flush the collected workspace rows (the barrier above made them visible)
+        if (S && stored > 0) {
+          double *dst     = S + (nt + r + 1 - SR) * (int64_t)(J * J);
+          const int count = stored * J * J;
+          if (swide) {
+            for (int e = 2 * c; e < count; e += 2 * G) *reinterpret_cast<double2 *>(dst + e) = *reinterpret_cast<const double2 *>(sbuf + e);
+          } else {
+            for (int e = c; e < count; e += G) dst[e] = sbuf[e];
+          }
+        }
+        stored = 0;
+        __syncwarp();
+      }
     }
-    const double w_c = (v_c - tmp) / dn;
-    if (alive && act) W[n * J + c] = w_c;
-    double w[J];
-    gall<G, J>(w_c, w);
-    const double dw = dn * w_c;
-#pragma unroll
-    for (int j = 0; j < J; ++j) Sg[j] = fma(w[j], dw, Sg[j]);
+    __syncwarp();
+    issue(k + 2);
   }
 }
 
 // summary: lane c owns column c of A, C, Q (row-major element (j,c)); see factor.cuh for the recurrences
+// tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 template <int J>
 __global__ void __launch_bounds__(kGroupThreads) gfactor_summary_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;
+  constexpr int R  = FactorTile<J>::R;
+  constexpr int JE = (J + 1) & ~1;
+  constexpr int oV = R * J, oT = 2 * R * J, oA = oT + R + 2;
+  constexpr int TB = (oA + R + 1) & ~1;
+  constexpr int GS = GTileStride<G, TB, 2>::value;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ __align__(16) double sprop[GP * R * JE];
+  __shared__ __align__(16) double sxch[GP * 4 * JE];
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
   const int64_t unit   = (int64_t)blockIdx.x * GP + gin;
   const bool has       = unit < g.batch * g.C;
   const bool act       = has && c < J;
+  const int cj         = c < J ? c : 0;
   const int64_t chunk  = has ? unit % g.C : 0, b = has ? unit / g.C : 0;
   const int64_t n0     = chunk * g.L;
   const int64_t n1     = has ? (n0 + g.L < g.N ? n0 + g.L : g.N) : n0;
   const double *t      = g.t + b * g.t_bs;
   const int64_t NJ     = g.N * J;
   const double *a = g.a + b * g.N, *U = g.U + b * NJ, *V = g.V + b * NJ;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 4 * JE;
+  const GCopy<G> cp{c};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const double cc = act ? (g.c + b * g.c_bs)[c] : 0.0;
   double A[J], Cm[J], Q[J];  // column c
 #pragma unroll
@@ -112,52 +187,78 @@ __global__ void __launch_bounds__(kGroupThreads) gfactor_summary_kernel(FactorAr
     Cm[j] = 0.0;
     Q[j]  = 0.0;
   }
-  double tn = 0.0, tp = 0.0, an = 0.0, un = 0.0, vn = 0.0;
-  if (n0 < n1) {
-    tn = t[n0];
-    tp = n0 > 0 ? t[n0 - 1] : tn;
-    an = a[n0];
-    un = act ? U[n0 * J + c] : 0.0;
-    vn = act ? V[n0 * J + c] : 0.0;
-  }
-  const int trips = warp_max((int)(n1 - n0));
-  for (int i = 0; i < trips; ++i) {
-    const int64_t n  = n0 + i;
-    const bool live  = n < n1;
-    const double t_cur = tn, t_prev = tp, a_cur = live ? an : 1.0, u_c = live ? un : 0.0, v_c = live ? vn : 0.0;
-    if (n + 1 < n1) {
-      tn = t[n + 1];
-      an = a[n + 1];
-      un = act ? U[(n + 1) * J + c] : 0.0;
-      vn = act ? V[(n + 1) * J + c] : 0.0;
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = n0 + (int64_t)k * R;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb, U + lo * J, rows * J, wide);
+      cp.run(tb + oV, V + lo * J, rows * J, wide);
+      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.N);
+      cp.run(tb + oA, a + lo, rows, false);
     }
-    tp = t_cur;
-    // past the end of the chunk the row is the identity: p = 1, u = v = 0, a = 1
-    const double p_c = (n == 0 || !live) ? 1.0 : exp(cc * (t_prev - t_cur));
-    double p[J], u[J];
-    gall<G, J>(p_c, p);
-    gall<G, J>(u_c, u);
-    double q_c = 0.0, r_c = 0.0;
+    cp_async_commit();
+  };
+  issue(0);
+  issue(1);
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    if (c < J) {
 #pragma unroll
-    for (int j = 0; j < J; ++j) {
-      A[j] *= p[j];
-      Cm[j] *= p[j] * p_c;
-      q_c = fma(Cm[j], u[j], q_c);  // C symmetric: column c dotted with u = (C u)_c
-      r_c = fma(A[j], u[j], r_c);   // (A^T u)_c
+      for (int r = 0; r < R; ++r) pb[r * JE + c] = exp(cc * (tb[oT + r] - tb[oT + r + 1]));  // dt = 0 at n = 0
     }
-    const double gam  = a_cur + gsum<G>(u_c * q_c);
-    const double igam = 1.0 / gam;
-    const double g_c  = (q_c + v_c) * igam;
-    double gv[J], r[J];
-    gall<G, J>(g_c, gv);
-    gall<G, J>(r_c, r);
-    const double ggc = gam * g_c, rgc = r_c * igam;
+    __syncwarp();
 #pragma unroll
-    for (int j = 0; j < J; ++j) {
-      A[j]  = fma(-gv[j], r_c, A[j]);
-      Cm[j] = fma(-gv[j], ggc, Cm[j]);
-      Q[j]  = fma(r[j], rgc, Q[j]);
+    for (int r = 0; r < R; ++r) {
+      // past the end of the chunk the row is the identity: p = 1, u = v = 0, a = 1
+      const bool live = r < rows;
+      double p[J], u[J];
+      lds_row<J>(pb + r * JE, p);
+      lds_row<J>(tb + r * J, u);
+      const double p_c = (live && act) ? pb[r * JE + cj] : 1.0;
+      const double u_c = (live && act) ? tb[r * J + cj] : 0.0;
+      const double v_c = (live && act) ? tb[oV + r * J + cj] : 0.0;
+      const double a_n = live ? tb[oA + r] : 1.0;
+      double q_c = 0.0, r_c = 0.0;
+      if (live) {
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+          A[j] *= p[j];
+          Cm[j] *= p[j] * p_c;
+          q_c = fma(Cm[j], u[j], q_c);  // C symmetric: column c dotted with u = (C u)_c
+          r_c = fma(A[j], u[j], r_c);   // (A^T u)_c
+        }
+      }
+      const double gam  = a_n + gsum<G>(u_c * q_c);
+      const double igam = 1.0 / gam;
+      const double g_c  = (q_c + v_c) * igam;
+      double *xw = xch + (r & 1) * 2 * JE;
+      if (c < J) {
+        xw[c]      = g_c;
+        xw[JE + c] = r_c;
+      }
+      __syncwarp();
+      double gv[J], rv[J];
+      lds_row<J>(xw, gv);
+      lds_row<J>(xw + JE, rv);
+      const double ggc = gam * g_c, rgc = r_c * igam;
+      if (live) {
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+          A[j]  = fma(-gv[j], r_c, A[j]);
+          Cm[j] = fma(-gv[j], ggc, Cm[j]);
+          Q[j]  = fma(rv[j], rgc, Q[j]);
+        }
+      }
     }
+    __syncwarp();
+    issue(k + 2);
   }
   if (act) {
     double *e = g.leaves + (b * g.node_stride + chunk) * (int64_t)(3 * J * J);
