@@ -4,7 +4,7 @@
 namespace c2b {
 
 static void sizes_factor(int64_t N, int J, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb) {
-  *pl = make_plan(N, batch, 1);
+  *pl = make_plan(N, batch, 1, J);
   if (pl->C > 1) take_scan(ar, batch, pl->C, 3 * J * J, J * J, sb);
 }
 size_t scratch_factor(int64_t N, int J, int64_t batch) {
@@ -16,7 +16,7 @@ size_t scratch_factor(int64_t N, int J, int64_t batch) {
 }
 
 static void sizes_factor_rev(int64_t N, int J, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb, double **bc_part, double **bt_edge) {
-  *pl = make_plan(N, batch, 1);
+  *pl = make_plan(N, batch, 1, J);
   if (pl->C > 1) take_scan(ar, batch, pl->C, 2 * J * J, J * J, sb);
   *bc_part = ar.take<double>((size_t)batch * pl->C * J);
   *bt_edge = ar.take<double>((size_t)batch * pl->C);

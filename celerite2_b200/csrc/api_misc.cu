@@ -71,7 +71,25 @@ int64_t get_chunk_override() {
 
 // Chunks along N exist only to expose parallelism: batch * cols * C independent units should fill the GPU
 // (148 SMs x a few warps).  Short chunks would be dominated by the summary pass, so L >= 64.
-Plan make_plan(int64_t N, int64_t batch, int64_t cols) {
+//
+// For the lane-group kernels (K == 1, J > 0 given) the unit is a group of G(J) lanes and a CTA holds 64 / G groups.
+// Every CTA of an op must be resident at once or the last partial wave runs the whole chunk length again
+// (r01f profile: 1.14 waves cost factor_rev 25 %), and the heaviest of those kernels fits 6 CTAs per SM
+// (registers, shared memory).  So the default is 6 CTAs per SM exactly -- a grid that is a multiple of the SM count --
+// and never more than 8192 chunks (scan cost).
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+      n = v;
+    else
+      n = 148;
+  }
+  return n;
+}
+
+Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
   Plan pl;
   pl.N     = N;
   pl.batch = batch;
@@ -80,15 +98,22 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols) {
   if (ov > 0) {
     C = ov;
   } else {
-    static int64_t target = 0;
-    if (target == 0) {
+    static int64_t env_target = -1;
+    if (env_target < 0) {
       const char *s = getenv("C2B_TARGET_UNITS");
-      target        = s ? atoll(s) : 8192;
-      if (target < 1) target = 8192;
+      env_target    = s ? atoll(s) : 0;
+      if (env_target < 0) env_target = 0;
     }
-    const int64_t have   = batch * (cols > 0 ? cols : 1);
-    C                    = have >= target ? 1 : (target + have - 1) / have;
-    const int64_t maxC   = N / 64;
+    int64_t target = 8192;
+    if (J > 0 && cols <= 1) {
+      const int lanes      = J <= 2 ? 2 : (J <= 4 ? 4 : (J <= 8 ? 8 : (J <= 16 ? 16 : 32)));
+      const int64_t groups = (int64_t)sm_count() * 6 * (64 / lanes);
+      if (groups < target) target = groups;
+    }
+    if (env_target > 0) target = env_target;
+    const int64_t have = batch * (cols > 0 ? cols : 1);
+    C                  = have >= target ? 1 : target / have;
+    const int64_t maxC = N / 64;
     if (C > maxC) C = maxC;
   }
   if (C > N) C = N;
@@ -123,7 +148,7 @@ Scratch::~Scratch() {
 
 size_t scratch_general_matmul(int64_t M, int J, int K) {
   Arena ar = sizing_arena();
-  Plan pl  = make_plan(M, 1, K);
+  Plan pl  = make_plan(M, 1, K, 0);
   ScanBuffers sb;
   if (pl.C > 1) take_scan(ar, 1, pl.C, J + J * K, J * K, &sb);
   ar.take<double>((size_t)M * J * K);
@@ -159,7 +184,7 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
   rc = sc.init(scratch, scratch_bytes, scratch_general_matmul(M, J, K), stream);
   if (rc) return rc;
   Arena ar(sc.ptr, sc.bytes);
-  Plan pl = make_plan(M, 1, K);
+  Plan pl = make_plan(M, 1, K, 0);
   ScanBuffers sb;
   if (pl.C > 1) take_scan(ar, 1, pl.C, J + J * K, J * K, &sb);
   GmArgs g;

@@ -67,7 +67,7 @@ struct Plan {
   int64_t C;  // chunks per series
   int64_t L;  // points per chunk
 };
-Plan make_plan(int64_t N, int64_t batch, int64_t cols);
+Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J);
 int64_t get_chunk_override();
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }

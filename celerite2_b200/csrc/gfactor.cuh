@@ -18,7 +18,7 @@ struct FactorTile {
 
 // tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 template <int J>
-__global__ void __launch_bounds__(kGroupThreads) gfactor_apply_kernel(FactorArgs g) {
+__global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;  // groups per CTA
   constexpr int R  = FactorTile<J>::R;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kGroupThreads) gfactor_apply_kernel(FactorArgs
 // summary: lane c owns column c of A, C, Q (row-major element (j,c)); see factor.cuh for the recurrences
 // tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 template <int J>
-__global__ void __launch_bounds__(kGroupThreads) gfactor_summary_kernel(FactorArgs g) {
+__global__ void __launch_bounds__(kGroupThreads, 6) gfactor_summary_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;
   constexpr int R  = FactorTile<J>::R;

@@ -1,6 +1,6 @@
 // factor_rev: lane-group apply and summary kernels (compile-time J <= 16).  Lane c owns column c of G = sym(bS);
-// every row's inputs (for the apply pass including the J x J workspace row S[n]) arrive through the per-group
-// cp.async ring of group.cuh, DEPTH rows ahead of their use.
+// the inputs (for the apply pass including the J x J workspace rows) are staged in per-group tiles of rows
+// (group.cuh), the next tile in flight while the current one is consumed.
 // Recurrences: see factor.cuh.
 #pragma once
 #include "factor.cuh"
@@ -13,22 +13,26 @@ constexpr int kGroupThreadsR = 64;
 // WRITE: produce the outputs (apply); otherwise only carry G (and the J rows of the congruence matrix M, lane k
 // holding row k) through the chunk (summary).  The summary never needs the workspace S: S enters only bU and the
 // bc / bt terms (reverse.hpp:47-60), not the recursion of G.
+// tile buffer (rows walked downwards): [S[R*J*J]] U[R*J] W[R*J] bW[R*J] | t[R+2] d[R] bd[R]
 template <int J, bool WRITE>
-__global__ void __launch_bounds__(kGroupThreadsR) gfactor_rev_kernel(FactorRevArgs g) {
-  constexpr int G     = GroupOf<J>::G;
-  constexpr int GP    = kGroupThreadsR / G;
-  constexpr int JJ    = WRITE ? J * J : 0;
-  constexpr int oU    = JJ, oW = JJ + J, oB = JJ + 2 * J, oX = JJ + 3 * J;  // then d, bd, t_n, t_{n-1}
-  constexpr int ROWD  = (oX + 4 + 1) & ~1;
-  constexpr int DEPTH = (J <= 8) ? 4 : 2;
-  constexpr int JE    = (J + 1) & ~1;
-  __shared__ __align__(16) double sring[GP * GRing<G, ROWD, DEPTH>::kStride];
+__global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRevArgs g) {
+  constexpr int G  = GroupOf<J>::G;
+  constexpr int GP = kGroupThreadsR / G;
+  constexpr int R  = J <= 8 ? (WRITE ? 4 : 8) : 2;
+  constexpr int JE = (J + 1) & ~1;
+  constexpr int JJ = WRITE ? J * J : 0;
+  constexpr int oU = R * JJ, oW = oU + R * J, oB = oW + R * J, oT = oB + R * J, oD = oT + R + 2, oE = oD + R;
+  constexpr int TB = (oE + R + 1) & ~1;
+  constexpr int GS = GTileStride<G, TB, 2>::value;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ __align__(16) double sprop[GP * R * JE];
   __shared__ __align__(16) double sxch[GP * 2 * JE];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
   const bool has      = unit < g.batch * g.C;
   const bool act      = has && c < J;
+  const int cj        = c < J ? c : 0;
   const int64_t chunk = has ? unit % g.C : 0, b = has ? unit / g.C : 0;
   const int64_t n0    = chunk * g.L;
   const int64_t n1    = has ? (n0 + g.L < g.N ? n0 + g.L : g.N) : n0;
@@ -38,10 +42,11 @@ __global__ void __launch_bounds__(kGroupThreadsR) gfactor_rev_kernel(FactorRevAr
   const double *d = g.d + b * g.N, *bd = g.bd + b * g.N;
   double *bt = WRITE ? g.bt + b * g.N : nullptr, *ba = WRITE ? g.ba + b * g.N : nullptr;
   double *bU = WRITE ? g.bU + b * NJ : nullptr, *bV = WRITE ? g.bV + b * NJ : nullptr;
-  GRing<G, ROWD, DEPTH> ring{sring + gin * GRing<G, ROWD, DEPTH>::kStride, c};
-  double *xch         = sxch + gin * 2 * JE;
-  const bool s16      = WRITE && (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
-  const double cc     = act ? (g.c + b * g.c_bs)[c] : 0.0;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 2 * JE;
+  const GCopy<G> cp{c};
+  const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(bW)) & 15) == 0);
+  const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
+  const double cc  = act ? (g.c + b * g.c_bs)[c] : 0.0;
   double Gc[J];  // column c of G: Gc[j] = G(j, c)
   double Mr[J];  // summary: row c of M
 #pragma unroll
@@ -56,105 +61,111 @@ __global__ void __launch_bounds__(kGroupThreadsR) gfactor_rev_kernel(FactorRevAr
     for (int j = 0; j < J; ++j) Gc[j] = st[j * J + c];
   }
   double bc_acc = 0.0, pend = 0.0;
-  const int cnt   = (int)(n1 - n0);
-  const int trips = warp_max(cnt);
-  // rows are visited from n1-1 down to n0; trip i handles row n1-1-i
-  auto issue = [&](int i) {
-    if (i < cnt) {
-      const int64_t n = n1 - 1 - i;
-      if (WRITE) {
-        if (s16)
-          ring.copy16(i, 0, S + n * (int64_t)(J * J), J * J);
-        else
-          ring.copy(i, 0, S + n * (int64_t)(J * J), J * J);
-      }
-      if (c < J) {
-        ring.copy1(i, oU + c, U + n * J + c);
-        ring.copy1(i, oW + c, W + n * J + c);
-        ring.copy1(i, oB + c, bW + n * J + c);
-      }
-      for (int e = G - 1 - c; e < 4; e += G) {  // the idle lanes of the group first
-        const double *src = e == 0 ? d + n : (e == 1 ? bd + n : (e == 2 ? t + n : t + (n >= 1 ? n - 1 : n)));
-        ring.copy1(i, oX + e, src);
-      }
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  // tile k = rows [lo, lo + rows), the short last tile aligned to the end of the buffer
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = n1 - (int64_t)k * R - rows;
+      const int pad    = R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      if (WRITE) cp.run(tb + pad * J * J, S + lo * (int64_t)(J * J), rows * J * J, swide);
+      cp.run(tb + oU + pad * J, U + lo * J, rows * J, wide);
+      cp.run(tb + oW + pad * J, W + lo * J, rows * J, wide);
+      cp.run(tb + oB + pad * J, bW + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, g.N);
+      cp.run(tb + oD + pad, d + lo, rows, false);
+      cp.run(tb + oE + pad, bd + lo, rows, false);
     }
-    ring.commit();
+    cp_async_commit();
   };
+  issue(0);
+  issue(1);
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    const int64_t nt = n1 - 1 - (int64_t)k * R;  // first row of the tile in visiting order
+    if (c < J) {
 #pragma unroll
-  for (int s = 0; s < DEPTH; ++s) issue(s);
-  for (int i = 0; i < trips; ++i) {
-    const bool live = i < cnt;
-    const int64_t n = live ? n1 - 1 - i : 1;
-    const bool nb   = live && n >= 1;
-    ring.acquire();
-    const double *rb = ring.stage(i);
-    double w[J], u[J], Sn[J];  // Sn[j] = S_n(j, c)
-    lds_row<J>(rb + oU, u);
-    lds_row<J>(rb + oW, w);
-    if (WRITE) lds_row<J>(rb + (c < J ? J * c : 0), Sn);
-    const int cj       = c < J ? c : 0;
-    const double u_c   = act ? rb[oU + cj] : 0.0;
-    const double w_c   = act ? rb[oW + cj] : 0.0;
-    const double bw_c  = act ? rb[oB + cj] : 0.0;
-    const double d_n   = live ? rb[oX] : 1.0;
-    const double bd_n  = rb[oX + 1];
-    const double t_cur = rb[oX + 2], t_prev = rb[oX + 3];
-    ring.release();
-    issue(i + DEPTH);
-    double wG = 0.0;
-#pragma unroll
-    for (int j = 0; j < J; ++j) wG = fma(w[j], Gc[j], wG);
-    const double bv_c = fma(2.0, wG, bw_c / d_n);
-    // ba_n = bd_n + w G w^T - w . bV_n   (reverse.hpp:30-33), one reduction for both
-    const double ban = bd_n + gsum<G>(w_c * (wG - bv_c));
-    const double dt  = t_prev - t_cur;
-    const double p_c = nb ? exp(cc * dt) : 1.0;
-    const double y_c = fma(ban, u_c, bv_c);
-    if (act) {
-      xch[c]      = y_c;
-      xch[JE + c] = p_c;
-    }
-    if (WRITE && live) {
-      if (c == G - 1) ba[n] = ban;
-      if (act) bV[n * J + c] = bv_c;
+      for (int r = 0; r < R; ++r) {
+        const int s    = R - 1 - r;
+        pb[r * JE + c] = exp(cc * (tb[oT + s] - tb[oT + s + 1]));  // dt = t_{n-1} - t_n, 0 at n = 0
+      }
     }
     __syncwarp();
-    double y[J], p[J];
-    lds_row<J>(xch, y);
-    lds_row<J>(xch + JE, p);
-    double bp = 0.0, xs = 0.0;
-    if (nb) {
-      if (!WRITE) {
-        // M <- M T_n, lane c holding row c: r <- (r - (r.w) u) o p
-        double s = 0.0;
 #pragma unroll
-        for (int j = 0; j < J; ++j) s = fma(Mr[j], w[j], s);
+    for (int r = 0; r < R; ++r) {
+      const int s     = R - 1 - r;
+      const bool live = r < rows;
+      const int64_t n = nt - r;
+      const bool nb   = live && n >= 1;
+      double w[J], u[J], p[J], Sn[J];  // Sn[j] = S_n(j, c)
+      lds_row<J>(tb + oU + s * J, u);
+      lds_row<J>(tb + oW + s * J, w);
+      lds_row<J>(pb + r * JE, p);
+      if (WRITE) lds_row<J>(tb + s * J * J + J * cj, Sn);
+      const double u_c  = act ? tb[oU + s * J + cj] : 0.0;
+      const double w_c  = act ? tb[oW + s * J + cj] : 0.0;
+      const double bw_c = act ? tb[oB + s * J + cj] : 0.0;
+      const double p_c  = act ? pb[r * JE + cj] : 1.0;
+      const double d_n  = live ? tb[oD + s] : 1.0;
+      const double bd_n = tb[oE + s];
+      double wG = 0.0;
 #pragma unroll
-        for (int j = 0; j < J; ++j) Mr[j] = fma(-s, u[j], Mr[j]) * p[j];
+      for (int j = 0; j < J; ++j) wG = fma(w[j], Gc[j], wG);
+      const double bv_c = fma(2.0, wG, bw_c / d_n);
+      // ba_n = bd_n + w G w^T - w . bV_n   (reverse.hpp:30-33), one reduction for both
+      const double ban = bd_n + gsum<G>(w_c * (wG - bv_c));
+      const double y_c = fma(ban, u_c, bv_c);
+      double *xy = xch + (r & 1) * JE;
+      if (c < J) xy[c] = y_c;
+      if (WRITE && live) {
+        if (c == G - 1) ba[n] = ban;
+        if (act) bV[n * J + c] = bv_c;
       }
-      double gs = 0.0;
+      __syncwarp();
+      double y[J];
+      lds_row<J>(xy, y);
+      double bp = 0.0, xs = 0.0;
+      if (nb) {
+        if (!WRITE) {
+          // M <- M T_n, lane c holding row c: r <- (r - (r.w) u) o p
+          double sm = 0.0;
 #pragma unroll
-      for (int j = 0; j < J; ++j) {
-        Gc[j] -= 0.5 * (u[j] * y_c + u_c * y[j]);
-        if (WRITE) {
-          const double xj = fma(ban, u[j], y[j]);  // x = bV + 2 ba u = y + ba u
-          xs              = fma(xj, Sn[j], xs);
-          gs              = fma(Sn[j], Gc[j], gs);
+          for (int j = 0; j < J; ++j) sm = fma(Mr[j], w[j], sm);
+#pragma unroll
+          for (int j = 0; j < J; ++j) Mr[j] = fma(-sm, u[j], Mr[j]) * p[j];
+        }
+        double gs = 0.0;
+#pragma unroll
+        for (int j = 0; j < J; ++j) {
+          Gc[j] -= 0.5 * (u[j] * y_c + u_c * y[j]);
+          if (WRITE) {
+            const double xj = fma(ban, u[j], y[j]);  // x = bV + 2 ba u = y + ba u
+            xs              = fma(xj, Sn[j], xs);
+            gs              = fma(Sn[j], Gc[j], gs);
+          }
+        }
+        bp = 2.0 * p_c * gs;
+        if (WRITE) bc_acc = fma(tb[oT + s] - tb[oT + s + 1], bp, bc_acc);
+#pragma unroll
+        for (int j = 0; j < J; ++j) Gc[j] *= p[j] * p_c;
+      }
+      if (WRITE) {
+        const double fac = gsum<G>(cc * bp);  // bp = 0 on rows without a predecessor
+        if (live) {
+          if (act) bU[n * J + c] = nb ? -(xs * p_c) : 0.0;
+          if (c == 0) bt[n] = pend - fac;
+          pend = fac;
         }
       }
-      bp = 2.0 * p_c * gs;
-      if (WRITE) bc_acc = fma(dt, bp, bc_acc);
-#pragma unroll
-      for (int j = 0; j < J; ++j) Gc[j] *= p[j] * p_c;
     }
-    if (WRITE) {
-      const double fac = gsum<G>(cc * bp);  // bp = 0 on rows without a predecessor
-      if (live) {
-        if (act) bU[n * J + c] = nb ? -(xs * p_c) : 0.0;
-        if (c == 0) bt[n] = pend - fac;
-        pend = fac;
-      }
-    }
+    __syncwarp();
+    issue(k + 2);
   }
   if (WRITE) {
     if (act) g.bc_part[(b * g.C + chunk) * J + c] = bc_acc;

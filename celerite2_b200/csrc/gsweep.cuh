@@ -14,7 +14,7 @@ constexpr int kTileRows = 8;  // rows per staged tile (group.cuh)
 // ---- forward apply -----------------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] | t[R+2] y[R] z_old[R]
 template <int J, bool SOLVE, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS) gsweep_apply_kernel(SweepArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepArgs a) {
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_apply_kernel(SweepArgs 
 // ---- forward summary, solves: lane q carries column q ----------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] | t[R+2] y[R]; plus one R x J block per group for the propagators of the tile
 template <int J, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS) gsweep_summary_kernel(SweepArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(SweepArgs a) {
   constexpr int G  = GroupOf<J + 1>::G;  // J + 1 columns
   constexpr int GP = kGroupThreadsS / G;
   constexpr int R  = kTileRows;
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_summary_kernel(SweepArg
 // ---- reverse apply -----------------------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] F[R*J] | t[R+2] bZ[R] (Z or Y)[R]
 template <int J, bool SOLVE, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_apply_kernel(SweepRevArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(SweepRevArgs a) {
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_apply_kernel(SweepR
 // ---- reverse summary, solves -----------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] | t[R+2] bZ[R]; plus the R x J propagator block
 template <int J, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS) gsweep_rev_summary_kernel(SweepRevArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(SweepRevArgs a) {
   constexpr int G   = GroupOf<J + 1>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;

@@ -1,5 +1,5 @@
 timeout 600 python -m pytest tests -x -q -m gpu 2>&1 | tail -5
-for T in 8192 16384 32768; do
+for T in ${TS:-8192 16384 32768}; do
 C2B_TARGET_UNITS=$T python bench.py --steps 5 --no-cpu-baseline > gpurun_out/b_$T.json 2>gpurun_out/b_$T.err
 python - <<EOF
 import json
