@@ -160,37 +160,31 @@ C2B_DEV void wsolve_reg(int lane, const double *Mx, double *R) {
 template <class Mon>
 struct Coop;  // wsmem(J,K) doubles per warp; wcombine / wapply mirror Mon::combine / Mon::apply
 
+// The operands of wcombine / wapply live in shared memory (block-resident trees of scan.cuh) and are read in place;
+// `sm` is the warp's private scratch for intermediate products only.
 template <int JT>
 struct Coop<AffV<JT>> {
-  __host__ __device__ static int wsmem(int J, int) { return 2 * J * J; }
-  C2B_DEV static void wcombine(int lane, int J, int K, const double *e1, const double *e2, double *out, double *sm) {
+  __host__ __device__ static int wsmem(int, int) { return 0; }
+  C2B_DEV static void wcombine(int lane, int J, int K, const double *e1, const double *e2, double *out, double *) {
     const int JJ = J * J;
-    double *M1 = sm, *M2 = sm + JJ;
-    wcopy(lane, JJ, e1, M1);
-    wcopy(lane, JJ, e2, M2);
-    __syncwarp();
-    wmm<false, false>(lane, J, J, J, M2, J, M1, J, nullptr, 0, out, J);
+    wmm<false, false>(lane, J, J, J, e2, J, e1, J, nullptr, 0, out, J);  // M = M2 M1
     // b = M2 b1 + b2 : b is J x K with element (j,k) at [j + J*k]
     const double *b1 = e1 + JJ, *b2 = e2 + JJ;
     double *b = out + JJ;
     for (int e = lane; e < J * K; e += 32) {
       const int k = e / J, i = e - k * J;
       double s    = b2[e];
-      for (int j = 0; j < J; ++j) s = fma(M2[i * J + j], b1[j + J * k], s);
+      for (int j = 0; j < J; ++j) s = fma(e2[i * J + j], b1[j + J * k], s);
       b[e] = s;
     }
     __syncwarp();
   }
-  C2B_DEV static void wapply(int lane, int J, int K, const double *e, const double *sin, double *sout, double *sm) {
-    const int JJ = J * J;
-    double *M = sm;
-    wcopy(lane, JJ, e, M);
-    __syncwarp();
-    const double *b = e + JJ;
+  C2B_DEV static void wapply(int lane, int J, int K, const double *e, const double *sin, double *sout, double *) {
+    const double *b = e + J * J;
     for (int x = lane; x < J * K; x += 32) {
       const int k = x / J, i = x - k * J;
       double s    = b[x];
-      for (int j = 0; j < J; ++j) s = fma(M[i * J + j], sin[j + J * k], s);
+      for (int j = 0; j < J; ++j) s = fma(e[i * J + j], sin[j + J * k], s);
       sout[x] = s;
     }
     __syncwarp();
@@ -219,31 +213,24 @@ struct Coop<DiagV<JT>> {
 
 template <int JT>
 struct Coop<Cong<JT>> {
-  __host__ __device__ static int wsmem(int J, int) { return 5 * J * J; }
+  __host__ __device__ static int wsmem(int J, int) { return 2 * J * J; }
   C2B_DEV static void wcombine(int lane, int J, int, const double *e1, const double *e2, double *out, double *sm) {
     const int JJ = J * J;
-    double *M1 = sm, *M2 = sm + JJ, *B1 = sm + 2 * JJ, *T = sm + 3 * JJ, *R = sm + 4 * JJ;
-    wcopy(lane, JJ, e1, M1);
-    wcopy(lane, JJ, e2, M2);
-    wcopy(lane, JJ, e1 + JJ, B1);
+    double *T = sm, *R = sm + JJ;
+    wmm<false, false>(lane, J, J, J, e1, J, e2, J, nullptr, 0, out, J);     // M = M1 M2
+    wmm<false, false>(lane, J, J, J, e1 + JJ, J, e2, J, nullptr, 0, T, J);  // T = B1 M2
     __syncwarp();
-    wmm<false, false>(lane, J, J, J, M1, J, M2, J, nullptr, 0, out, J);  // M = M1 M2
-    wmm<false, false>(lane, J, J, J, B1, J, M2, J, nullptr, 0, T, J);    // T = B1 M2
-    __syncwarp();
-    wmm<true, false>(lane, J, J, J, M2, J, T, J, nullptr, 0, R, J);  // R = M2^T T
+    wmm<true, false>(lane, J, J, J, e2, J, T, J, nullptr, 0, R, J);  // R = M2^T T
     __syncwarp();
     wsym_add(lane, J, R, e2 + JJ, out + JJ);
     __syncwarp();
   }
   C2B_DEV static void wapply(int lane, int J, int, const double *e, const double *sin, double *sout, double *sm) {
     const int JJ = J * J;
-    double *M = sm, *G = sm + JJ, *T = sm + 2 * JJ, *R = sm + 3 * JJ;
-    wcopy(lane, JJ, e, M);
-    wcopy(lane, JJ, sin, G);
+    double *T = sm, *R = sm + JJ;
+    wmm<false, false>(lane, J, J, J, sin, J, e, J, nullptr, 0, T, J);  // T = G M
     __syncwarp();
-    wmm<false, false>(lane, J, J, J, G, J, M, J, nullptr, 0, T, J);
-    __syncwarp();
-    wmm<true, false>(lane, J, J, J, M, J, T, J, nullptr, 0, R, J);
+    wmm<true, false>(lane, J, J, J, e, J, T, J, nullptr, 0, R, J);  // R = M^T T
     __syncwarp();
     wsym_add(lane, J, R, e + JJ, sout);
     __syncwarp();
@@ -252,23 +239,19 @@ struct Coop<Cong<JT>> {
 
 template <int JT>
 struct Coop<Lft<JT>> {
-  __host__ __device__ static int wsmem(int J, int) { return 13 * J * J; }
+  __host__ __device__ static int wsmem(int J, int) { return 7 * J * J; }
   C2B_DEV static void wcombine(int lane, int J, int, const double *e1, const double *e2, double *out, double *sm) {
     const int JJ = J * J;
-    double *A1 = sm, *C1 = sm + JJ, *A2 = sm + 2 * JJ, *Q2 = sm + 3 * JJ, *MX = sm + 4 * JJ;
-    double *R = sm + 5 * JJ;  // J x 2J : [A1 | C1] -> [X1 | X2]
-    double *T2 = sm + 7 * JJ, *T3 = sm + 8 * JJ, *RC = sm + 9 * JJ, *RQ = sm + 10 * JJ;
-    wcopy(lane, JJ, e1, A1);
-    wcopy(lane, JJ, e1 + JJ, C1);
-    wcopy(lane, JJ, e2, A2);
-    wcopy(lane, JJ, e2 + 2 * JJ, Q2);
-    __syncwarp();
+    const double *A1 = e1, *C1 = e1 + JJ, *A2 = e2, *Q2 = e2 + 2 * JJ;
+    double *MX = sm;
+    double *R  = sm + JJ;  // J x 2J : [A1 | C1] -> [X1 | X2]
+    double *T2 = sm + 3 * JJ, *T3 = sm + 4 * JJ, *RC = sm + 5 * JJ, *RQ = sm + 6 * JJ;
     // MX = I + C1 Q2 ; R = [A1 | C1]
     for (int e = lane; e < JJ; e += 32) {
       const int i = e / J, j = e - i * J;
       double s    = (i == j) ? 1.0 : 0.0;
       for (int k = 0; k < J; ++k) s = fma(C1[i * J + k], Q2[k * J + j], s);
-      MX[e]            = s;
+      MX[e]                = s;
       R[i * 2 * J + j]     = A1[e];
       R[i * 2 * J + J + j] = C1[e];
     }
@@ -288,11 +271,8 @@ struct Coop<Lft<JT>> {
   }
   C2B_DEV static void wapply(int lane, int J, int, const double *e, const double *sin, double *sout, double *sm) {
     const int JJ = J * J;
-    double *A = sm, *Q = sm + JJ, *X = sm + 2 * JJ, *MX = sm + 3 * JJ, *Z = sm + 4 * JJ, *T = sm + 5 * JJ, *R = sm + 6 * JJ;
-    wcopy(lane, JJ, e, A);
-    wcopy(lane, JJ, e + 2 * JJ, Q);
-    wcopy(lane, JJ, sin, X);
-    __syncwarp();
+    const double *A = e, *Q = e + 2 * JJ, *X = sin;
+    double *MX = sm, *Z = sm + JJ, *T = sm + 2 * JJ, *R = sm + 3 * JJ;
     for (int x = lane; x < JJ; x += 32) {
       const int i = x / J, j = x - i * J;
       double s    = (i == j) ? 1.0 : 0.0;

@@ -152,60 +152,121 @@ C2B_DEV void wdown_node(int lane, int J, int K, const Levels &lv, const double *
   __syncwarp();
 }
 
-constexpr int kCoopLeaves = 32;  // nodes per block
-constexpr int kCoopLevels = 5;
-constexpr int kCoopWarps  = 16;  // warps per CTA (fewer when the per-warp shared memory is large): one combine each per round
+// ---- block-resident tree kernels ----------------------------------------------------------------------------------
+// One CTA owns a block of LB = 2^nlev nodes of level `lb` and the nlev tree levels above them.  The block's nodes are
+// loaded into shared memory once (coalesced), every level is one round of independent warp-cooperative combines
+// from shared memory to shared memory separated by CTA barriers, and the new nodes go back to global memory in one
+// coalesced pass at the end: one L2 round trip per launch instead of three per level (r01f: 2.5 us per level for a
+// 6 x 6 product).  The down-sweep mirrors that with a tree of states; the launch that holds the top of the tree
+// does both directions without leaving shared memory.
+//
+// Local tree layout: local level q (global level lb + q) has LB >> q slots starting at slot 2 LB - (2 LB >> q).
+struct BlockTree {
+  int nlev, LB, nl;     // levels per launch, 2^nlev, levels actually present above lb in this launch
+  int64_t blk, b;       // block index within the series, series
+  int cnt[8];           // valid nodes per local level
+  C2B_DEV int off(int q) const { return 2 * LB - ((2 * LB) >> q); }
+};
 
-// One CTA per (series, block of 32 nodes at level `lb`): builds levels lb+1 .. min(lb+5, top).  Every level is one
-// round of independent warp-cooperative combines, separated by CTA barriers.
+C2B_DEV BlockTree make_block_tree(const Levels &lv, int lb, int nlev) {
+  BlockTree bt;
+  bt.nlev            = nlev;
+  bt.LB              = 1 << nlev;
+  const int64_t nblk = (lv.count[lb] + bt.LB - 1) / bt.LB;
+  bt.b               = blockIdx.x / nblk;
+  bt.blk             = blockIdx.x % nblk;
+  const int top      = lv.nlev - 1;
+  bt.nl              = top - lb < nlev ? top - lb : nlev;
+  const int64_t rem  = lv.count[lb] - bt.blk * bt.LB;
+  bt.cnt[0]          = rem < bt.LB ? (int)rem : bt.LB;
+  for (int q = 1; q <= bt.nl; ++q) bt.cnt[q] = (bt.cnt[q - 1] + 1) >> 1;
+  return bt;
+}
+
 template <class Mon>
-__global__ void __launch_bounds__(kCoopWarps * 32) scan_up_block(int J_, int K, int64_t batch, Levels lv, int lb, double *nodes_all) {
-  const int J = Mon::kJT ? Mon::kJT : J_;
-  extern __shared__ double sm_all[];
-  const int wsm      = Coop<Mon>::wsmem(J, K);
-  const int wib      = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double *sm         = sm_all + (size_t)wib * wsm;
-  const int64_t nblk = (lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves;
-  const int64_t b = blockIdx.x / nblk, blk = blockIdx.x % nblk;
-  const int es  = Mon::esize(J, K);
-  double *nodes = nodes_all + b * lv.total * es;
-  const int top = lv.nlev - 1 < lb + kCoopLevels ? lv.nlev - 1 : lb + kCoopLevels;
-  for (int l = lb + 1; l <= top; ++l) {
-    const int sh        = l - lb;
-    const int64_t first = (blk * kCoopLeaves) >> sh;
-    for (int r = wib; r < (kCoopLeaves >> sh); r += (int)(blockDim.x >> 5))
-      if (first + r < lv.count[l]) wup_node<Mon>(lane, J, K, lv, nodes, es, l, first + r, sm);
+C2B_DEV void block_up(const BlockTree &bt, int J, int K, int es, double *tree, double *sm, int wib, int lane, int nwarps) {
+  for (int q = 1; q <= bt.nl; ++q) {
+    for (int r = wib; r < bt.cnt[q]; r += nwarps) {
+      const double *left = tree + (size_t)(bt.off(q - 1) + 2 * r) * es;
+      double *out        = tree + (size_t)(bt.off(q) + r) * es;
+      if (2 * r + 1 < bt.cnt[q - 1]) {
+        Coop<Mon>::wcombine(lane, J, K, left, left + es, out, sm);
+      } else {
+        wcopy(lane, es, left, out);
+        __syncwarp();
+      }
+    }
     __syncthreads();
   }
 }
 
-// Mirror image: states of levels min(lb+5, top) .. lb+1 are pushed down to level lb.  The CTA that owns the top of the
-// tree seeds it with the initial state.
+// states of local level bt.nl must be in `st`; fills the levels below
 template <class Mon>
-__global__ void __launch_bounds__(kCoopWarps * 32) scan_down_block(int J_, int K, int64_t batch, Levels lv, int lb,
-                                                                    const double *nodes_all, double *states_all, const double *init) {
-  const int J = Mon::kJT ? Mon::kJT : J_;
-  extern __shared__ double sm_all[];
-  const int wsm      = Coop<Mon>::wsmem(J, K);
-  const int wib      = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  double *sm         = sm_all + (size_t)wib * wsm;
-  const int64_t nblk = (lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves;
-  const int64_t b = blockIdx.x / nblk, blk = blockIdx.x % nblk;
-  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
-  const double *nodes = nodes_all + b * lv.total * es;
-  double *states      = states_all + b * lv.total * ss;
-  const int top       = lv.nlev - 1 < lb + kCoopLevels ? lv.nlev - 1 : lb + kCoopLevels;
-  if (top == lv.nlev - 1) {
-    double *st = states + lv.off[top] * ss;
-    for (int i = threadIdx.x; i < ss; i += blockDim.x) st[i] = init ? init[b * ss + i] : 0.0;
+C2B_DEV void block_down(const BlockTree &bt, int J, int K, int es, int ss, const double *tree, double *st, double *sm, int wib, int lane,
+                        int nwarps) {
+  for (int q = bt.nl; q >= 1; --q) {
+    for (int r = wib; r < bt.cnt[q]; r += nwarps) {
+      const double *sin = st + (size_t)(bt.off(q) + r) * ss;
+      double *s0        = st + (size_t)(bt.off(q - 1) + 2 * r) * ss;
+      wcopy(lane, ss, sin, s0);
+      if (2 * r + 1 < bt.cnt[q - 1]) Coop<Mon>::wapply(lane, J, K, tree + (size_t)(bt.off(q - 1) + 2 * r) * es, sin, s0 + ss, sm);
+      __syncwarp();
+    }
     __syncthreads();
   }
-  for (int l = top; l > lb; --l) {
-    const int sh        = l - lb;
-    const int64_t first = (blk * kCoopLeaves) >> sh;
-    for (int r = wib; r < (kCoopLeaves >> sh); r += (int)(blockDim.x >> 5))
-      if (first + r < lv.count[l]) wdown_node<Mon>(lane, J, K, lv, nodes, states, es, ss, l, first + r, sm);
+}
+
+constexpr int kCoopThreadsMax = 512;
+
+// DIR: 0 = up only, 1 = down only, 2 = up then down (the launch that contains the top of the tree)
+template <class Mon, int DIR>
+__global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int64_t batch, Levels lv, int lb, int nlev, double *nodes_all,
+                                                             double *states_all, const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;
+  extern __shared__ __align__(16) double sm_all[];
+  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
+  const int wsm    = Coop<Mon>::wsmem(J, K);
+  const int nwarps = blockDim.x >> 5, wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const BlockTree bt = make_block_tree(lv, lb, nlev);
+  const int slots    = 2 * bt.LB - 1;
+  double *tree = sm_all;                                         // slots * es
+  double *st   = tree + (size_t)slots * es;                      // slots * ss (DIR >= 1)
+  double *sm   = st + (DIR >= 1 ? (size_t)slots * ss : 0) + (size_t)wib * wsm;
+  double *nodes  = nodes_all + bt.b * lv.total * es;
+  double *states = DIR >= 1 ? states_all + bt.b * lv.total * ss : nullptr;
+  // load: level lb nodes (up) / all present local levels below the top one (down)
+  const int qload = DIR == 1 ? bt.nl - 1 : 0;
+  for (int q = 0; q <= qload; ++q) {
+    const double *src = nodes + (lv.off[lb + q] + ((bt.blk * bt.LB) >> q)) * es;
+    double *dst       = tree + (size_t)bt.off(q) * es;
+    const int n       = bt.cnt[q] * es;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = src[e];
+  }
+  if (DIR == 1) {
+    const double *src = states + (lv.off[lb + bt.nl] + ((bt.blk * bt.LB) >> bt.nl)) * ss;
+    double *dst       = st + (size_t)bt.off(bt.nl) * ss;
+    for (int e = threadIdx.x; e < bt.cnt[bt.nl] * ss; e += blockDim.x) dst[e] = src[e];
+  }
+  __syncthreads();
+  if (DIR != 1) {
+    block_up<Mon>(bt, J, K, es, tree, sm, wib, lane, nwarps);
+    for (int q = 1; q <= bt.nl; ++q) {
+      double *dst       = nodes + (lv.off[lb + q] + ((bt.blk * bt.LB) >> q)) * es;
+      const double *src = tree + (size_t)bt.off(q) * es;
+      const int n       = bt.cnt[q] * es;
+      for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = src[e];
+    }
+  }
+  if (DIR == 2) {
+    // this CTA holds the root: seed it
+    double *dst = st + (size_t)bt.off(bt.nl) * ss;
+    for (int e = threadIdx.x; e < ss; e += blockDim.x) dst[e] = init ? init[bt.b * ss + e] : 0.0;
     __syncthreads();
+  }
+  if (DIR >= 1) {
+    block_down<Mon>(bt, J, K, es, ss, tree, st, sm, wib, lane, nwarps);
+    double *dst = states + (lv.off[lb] + bt.blk * bt.LB) * ss;
+    for (int e = threadIdx.x; e < bt.cnt[0] * ss; e += blockDim.x) dst[e] = st[e];
   }
 }
 
@@ -224,29 +285,44 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop) {
-    const int wsm     = Coop<Mon>::wsmem(J, K);
-    int nwarps = kCoopWarps;
-    while (nwarps > 1 && (size_t)nwarps * wsm * sizeof(double) > 200 * 1024) nwarps >>= 1;
-    const size_t smem = (size_t)nwarps * wsm * sizeof(double);
-    if (smem > 48 * 1024) {
-      C2B_CUDA(cudaFuncSetAttribute(scan_up_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      C2B_CUDA(cudaFuncSetAttribute(scan_down_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int es = Mon::esize(J, K), ss = Mon::ssize(J, K), wsm = Coop<Mon>::wsmem(J, K);
+    // levels per launch / warps per CTA: the largest configuration whose shared memory (sized for the launch that
+    // holds nodes and states) lets two CTAs share an SM
+    static const int cand[][2] = {{5, 16}, {5, 8}, {4, 8}, {4, 4}, {3, 4}, {2, 2}, {1, 1}};
+    int nlev = 1, nwarps = 1;
+    size_t smem = 0;
+    for (auto &cd : cand) {
+      const size_t slots = (size_t)(2 << cd[0]) - 1;
+      smem               = (slots * (es + ss) + (size_t)cd[1] * wsm) * sizeof(double);
+      nlev               = cd[0];
+      nwarps             = cd[1];
+      if (smem <= 110 * 1024) break;
+    }
+    if (smem > 220 * 1024) {
+      set_error("scan: summary element too large for the block-resident tree (%zu bytes of shared memory)", smem);
+      return C2B_ERR_INVALID_ARGUMENT;
+    }
+    static bool attr_done[64] = {};  // per instantiation and device
+    int dev = 0;
+    C2B_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+      C2B_CUDA(cudaFuncSetAttribute(scan_block<Mon, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      C2B_CUDA(cudaFuncSetAttribute(scan_block<Mon, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      C2B_CUDA(cudaFuncSetAttribute(scan_block<Mon, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+      if (dev >= 0 && dev < 64) attr_done[dev] = true;
     }
     const int top = lv.nlev - 1;
     int bases[kMaxLevels], nb = 0;
-    for (int lb = 0; lb < top || nb == 0; lb += kCoopLevels) bases[nb++] = lb;
-    for (int q = 0; q < nb; ++q) {
-      const int lb        = bases[q];
-      const unsigned grid = (unsigned)(batch * ((lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves));
-      if (lb < top)
-        C2B_LAUNCH("scan_up_block", stream, scan_up_block<Mon><<<grid, nwarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes));
-    }
-    for (int q = nb - 1; q >= 0; --q) {
-      const int lb        = bases[q];
-      const unsigned grid = (unsigned)(batch * ((lv.count[lb] + kCoopLeaves - 1) / kCoopLeaves));
+    for (int lb = 0; lb < top || nb == 0; lb += nlev) bases[nb++] = lb;
+    auto grid_of = [&](int lb) { return (unsigned)(batch * ((lv.count[lb] + (1 << nlev) - 1) >> nlev)); };
+    for (int q = 0; q + 1 < nb; ++q)
+      C2B_LAUNCH("scan_up_block", stream,
+                 (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, batch, lv, bases[q], nlev, nodes, states, init)));
+    C2B_LAUNCH("scan_top_block", stream,
+               (scan_block<Mon, 2><<<grid_of(bases[nb - 1]), nwarps * 32, smem, stream>>>(J, K, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
+    for (int q = nb - 2; q >= 0; --q)
       C2B_LAUNCH("scan_down_block", stream,
-                 scan_down_block<Mon><<<grid, nwarps * 32, smem, stream>>>(J, K, batch, lv, lb, nodes, states, init));
-    }
+                 (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, batch, lv, bases[q], nlev, nodes, states, init)));
     return C2B_OK;
   } else {
   const int threads  = 128;  // 4 warps
