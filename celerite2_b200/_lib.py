@@ -19,7 +19,7 @@ OP_IDS = {
     "solve_lower_rev": 6, "solve_upper_rev": 7, "matmul_lower_rev": 8, "matmul_upper_rev": 9,
     "general_matmul": 10, "assemble_rev": 11,
 }
-SHARED_T, SHARED_C, SHARED_Y = 1, 2, 4
+SHARED_T, SHARED_C, SHARED_Y, ACCUMULATE = 1, 2, 4, 8
 
 # name -> argument types (return type is int unless listed in _RESTYPE); mirrors include/celerite2_b200.h
 _SIGS = {

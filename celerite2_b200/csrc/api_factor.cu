@@ -96,6 +96,7 @@ int c2b_factor_rev(int64_t N, int32_t J, int64_t batch, const double *t, const d
   g.c_bs = (flags & C2B_SHARED_C) ? 0 : J;
   g.bc_part = bc_part;
   g.bt_edge = bt_edge;
+  g.acc     = (flags & C2B_ACCUMULATE) ? 1 : 0;
 #define CALL(JT) rc = launch_factor_rev<JT>(g, sb, bc, stream)
   C2B_DISPATCH_J_FACTOR(J, CALL)
 #undef CALL

@@ -60,6 +60,7 @@ struct FactorRevArgs {
   const double *carry;
   int64_t node_stride;
   double *bc_part, *bt_edge;
+  int acc;  // C2B_ACCUMULATE: bt, bc, bU are added to
 };
 
 template <int JT, bool SOLVE, bool LOWER>

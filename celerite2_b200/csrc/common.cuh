@@ -202,6 +202,15 @@ struct RowPipe {
   }
 };
 
+// Store or accumulate an output element.  Every element is touched by exactly one thread per launch, so the
+// accumulate form is a fire-and-forget reduction (no value returned, nothing waits for it).
+C2B_DEV void out_store(double *p, double v, bool acc) {
+  if (acc)
+    atomicAdd(p, v);
+  else
+    *p = v;
+}
+
 // First failing row of factor(): keep the smallest positive index (0 = success).
 C2B_DEV void record_failure(int64_t *status, int64_t n) {
   if (!status) return;

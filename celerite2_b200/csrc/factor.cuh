@@ -255,7 +255,7 @@ template <int JT, bool WRITE, bool WITHM = false>
 C2B_DEV void factor_rev_rows(int J, int64_t N, int64_t n0, int64_t n1, const double *t, const double *cj, const unsigned *dup,
                              const double *U, const double *d, const double *W, const double *S, const double *bd, const double *bW,
                              double *bt, double *ba, double *bU, double *bV, double *G, double *bc_acc, double *edge_out, double *smem,
-                             double *Mr = nullptr) {
+                             double *Mr = nullptr, bool acc = false) {
   constexpr int MJ = Width<JT>::MAXJ;
   RowPipe<(JT > 0), FactorRevRow<JT>::ROWD, kFactorRevSlots> rp;
   rp.init(smem);
@@ -346,7 +346,7 @@ C2B_DEV void factor_rev_rows(int J, int64_t N, int64_t n0, int64_t n1, const dou
           gs               = fma(sjk, G[j * J + k], gs);
         }
         if (WRITE) {
-          bU[n * J + k]   = -(xs * p[k]);
+          out_store(bU + n * J + k, -(xs * p[k]), acc);
           const double bp = 2.0 * p[k] * gs;
           bc_acc[k]       = fma(dt, bp, bc_acc[k]);
           fac             = fma(cj[k], bp, fac);
@@ -358,14 +358,16 @@ C2B_DEV void factor_rev_rows(int J, int64_t N, int64_t n0, int64_t n1, const dou
         for (int j = 0; j < J; ++j) G[k * J + j] *= p[k] * p[j];
       }
       if (WRITE) {
-        bt[n] = pend - fac;
-        pend  = fac;
+        out_store(bt + n, pend - fac, acc);
+        pend = fac;
       }
     } else if (WRITE) {
-      C2B_UNROLL_J
-      for (int j = 0; j < J; ++j) bU[j] = 0.0;
-      bt[0] = pend;
-      pend  = 0.0;
+      if (!acc) {
+        C2B_UNROLL_J
+        for (int j = 0; j < J; ++j) bU[j] = 0.0;
+      }
+      out_store(bt, pend, acc);
+      pend = 0.0;
     }
     rp.release();
   }
@@ -401,7 +403,8 @@ __global__ void factor_rev_apply_kernel(FactorRevArgs g) {
   }
   double edge = 0.0;
   factor_rev_rows<JT, true>(J, g.N, n0, n1, t, cj, dup, g.U + b * NJ, g.d + b * g.N, g.W + b * NJ, g.S + b * NJ * J, g.bd + b * g.N,
-                            g.bW + b * NJ, g.bt + b * g.N, g.ba + b * g.N, g.bU + b * NJ, g.bV + b * NJ, G, bc_acc, &edge, c2b_ring);
+                            g.bW + b * NJ, g.bt + b * g.N, g.ba + b * g.N, g.bU + b * NJ, g.bV + b * NJ, G, bc_acc, &edge, c2b_ring, nullptr,
+                            g.acc != 0);
   double *bcp = g.bc_part + (b * g.C + chunk) * J;
   C2B_UNROLL_J
   for (int j = 0; j < J; ++j) bcp[j] = bc_acc[j];

@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       if (WRITE) {
         const double fac = gsum<G>(cc * bp);  // bp = 0 on rows without a predecessor
         if (live) {
-          if (act) bU[n * J + c] = nb ? -(xs * p_c) : 0.0;
-          if (c == 0) bt[n] = pend - fac;
+          if (act) out_store(bU + n * J + c, nb ? -(xs * p_c) : 0.0, g.acc);
+          if (c == 0) out_store(bt + n, pend - fac, g.acc);
           pend = fac;
         }
       }

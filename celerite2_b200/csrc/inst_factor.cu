@@ -93,7 +93,7 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
     }
     C2B_LAUNCH("gfactor_rev_apply_kernel", stream, gfactor_rev_kernel<JT, true><<<grid, kGroupThreadsR, 0, stream>>>(g));
     C2B_LAUNCH("rev_finalize_kernel", stream,
-               rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc));
+               rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
   }
   return C2B_OK;
 }
@@ -117,7 +117,7 @@ int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaS
   rcs = staged_shape(factor_rev_apply_kernel<JT>, g.batch * g.C, JT > 0, kFactorRevSlots, FactorRevRow<JT>::ROWD, &grid, &block, &smem);
   if (rcs) return rcs;
   C2B_LAUNCH("factor_rev_apply_kernel", stream, factor_rev_apply_kernel<JT><<<grid, block, smem, stream>>>(g));
-  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc));
+  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
   return C2B_OK;
 }
 

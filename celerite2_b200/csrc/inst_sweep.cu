@@ -49,7 +49,7 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
     C2B_LAUNCH("gsweep_rev_apply_kernel", stream, gsweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
     C2B_LAUNCH("rev_finalize_kernel", stream,
-               rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc));
+               rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   }
   return C2B_OK;
 }
@@ -142,7 +142,7 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
                      &smem);
   if (rcs) return rcs;
   C2B_LAUNCH("sweep_rev_apply_kernel", stream, sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
-  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc));
+  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   return C2B_OK;
 }
 

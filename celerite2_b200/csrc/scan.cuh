@@ -344,7 +344,8 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
 //   descending == true  (lower / factor_rev): chunk k owes bt[n0_k - 1]
 //   descending == false (upper)             : chunk k owes bt[n1_k]
 static __global__ void __launch_bounds__(1024) rev_finalize_kernel(int64_t N, int64_t C, int64_t L, int J, bool descending,
-                                                                   const double *bc_part, const double *bt_edge, double *bt, double *bc) {
+                                                                   const double *bc_part, const double *bt_edge, double *bt, double *bc,
+                                                                   bool acc_bc) {
   const int64_t b = blockIdx.y;
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < C) {
@@ -367,7 +368,7 @@ static __global__ void __launch_bounds__(1024) rev_finalize_kernel(int64_t N, in
       double v = lane < nw ? sh[lane] : 0.0;
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) bc[b * J + j] = v;
+      if (lane == 0) bc[b * J + j] = acc_bc ? bc[b * J + j] + v : v;
     }
     __syncthreads();
   }

@@ -44,10 +44,7 @@ def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grad
     N = diag.shape[-1]
     ll = -0.5 * (out[..., 0] + out[..., 1] + N * math.log(2 * math.pi))
     bt, bc, bU, bW, bY = ops.solve_lower_rev(t, c, U, W, Y, Z, F, bz.unsqueeze(-1))
-    bt2, bc2, ba, bU2, bV = ops.factor_rev(t, c, a, U, V, d, W, S, bd, bW)
-    ops.add_inplace(bU2, bU)
-    ops.add_inplace(bc2, bc)
-    ops.add_inplace(bt2, bt)
+    _, _, ba, _, bV = ops.factor_rev(t, c, a, U, V, d, W, S, bd, bW, accumulate_into=(bt, bc, bU))
     g = ops.get_celerite_matrices_rev(*coeffs, t, bc, ba, bU, bV, b_x=bt, layout=layout, want_diag=want_data_grads)
     res = dict(loglike=ll, status=status, grads=dict(zip(COEFF_NAMES, g[:6])))
     if want_data_grads:

@@ -127,19 +127,31 @@ def factor(t, c, a, U, V, d=None, W=None, workspace=True, status=None):
     return d, W, S, status
 
 
-def factor_rev(t, c, a, U, V, d, W, S, bd, bW):
-    """-> (bt, bc, ba, bU, bV)"""
+def factor_rev(t, c, a, U, V, d, W, S, bd, bW, accumulate_into=None):
+    """-> (bt, bc, ba, bU, bV).  accumulate_into = (bt, bc, bU): add the cotangents of t, c and U to these arrays (those
+    solve_*_rev filled) instead of returning fresh ones (C2B_ACCUMULATE)."""
     t, c, U, d, W, S, bd, bW = [_f64(v, "arg") for v in (t, c, U, d, W, S, bd, bW)]
     batch, N, J = _batch_of(U)
     dev = U.device
     lead = U.shape[:-2]
-    bt = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
-    bc = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
-    ba = torch.empty_like(bt)
-    bU, bV = torch.empty_like(U), torch.empty_like(U)
+    extra = 0
+    if accumulate_into is not None:
+        bt, bc, bU = accumulate_into
+        for v in (bt, bc, bU):
+            if _f64(v, "accumulate_into") is not v:
+                raise ValueError("accumulate_into: arrays must be contiguous (they are updated in place)")
+        if bt.shape != lead + (N,) or bc.shape != lead + (J,) or bU.shape != U.shape:
+            raise ValueError("accumulate_into: shapes must be those of bt, bc, bU")
+        extra = _lib.ACCUMULATE
+        bV = torch.empty_like(U)
+    else:
+        bt = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
+        bc = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
+        bU, bV = torch.empty_like(U), torch.empty_like(U)
+    ba = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
     sp, sb = _get_scratch("factor_rev", N, 0, J, 1, batch, dev)
     check(lib.c2b_factor_rev(N, J, batch, _ptr(t), _ptr(c), _ptr(a), _ptr(U), _ptr(V), _ptr(d), _ptr(W), _ptr(S), _ptr(bd), _ptr(bW),
-                             _ptr(bt), _ptr(bc), _ptr(ba), _ptr(bU), _ptr(bV), _flags(batch, t, c), sp, sb, _stream()))
+                             _ptr(bt), _ptr(bc), _ptr(ba), _ptr(bU), _ptr(bV), _flags(batch, t, c) | extra, sp, sb, _stream()))
     return bt, bc, ba, bU, bV
 
 

@@ -39,6 +39,7 @@ extern "C" {
 #define C2B_SHARED_T 1 /* t has shape (N) for all series          */
 #define C2B_SHARED_C 2 /* c (and the coefficient vectors of the assembly) are shared */
 #define C2B_SHARED_Y 4 /* Y (or y) has no batch dimension          */
+#define C2B_ACCUMULATE 8 /* c2b_factor_rev only: add to bt, bc and bU instead of overwriting them */
 
 #define C2B_MAX_J 32
 
@@ -117,8 +118,11 @@ int c2b_factor(int64_t N, int32_t J, int64_t batch, const double *t, const doubl
 
 /*
  * Reverse mode of factor.  Replaces celerite2::core::factor_rev, c++/include/celerite2/reverse.hpp:10-85.
- * a and V are accepted for signature parity and never read (reverse.hpp:29-30).  All outputs are overwritten.
- * bc has shape (batch,J) even when c is shared.
+ * a and V are accepted for signature parity and never read (reverse.hpp:29-30).  All outputs are overwritten,
+ * unless flags has C2B_ACCUMULATE: then bt, bc and bU -- the cotangents of inputs that other operators of a
+ * pipeline read as well (t, c, U) -- are added to, so that the caller can pass the arrays solve_*_rev filled and
+ * skip three separate additions (what an autodiff framework does after the reference's factor_rev; no reference
+ * counterpart).  ba and bV are always overwritten.  bc has shape (batch,J) even when c is shared.
  */
 int c2b_factor_rev(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U,
                    const double *V, const double *d, const double *W, const double *S, const double *bd, const double *bW,

@@ -158,3 +158,32 @@ def test_full_size_round_trips_and_gradient_consistency(env):
     fd = float((lp - lm).item()) / (2 * h)
     an = sum(float((r["grads"][nm] * dv).sum().item()) for nm, dv in zip(gp.COEFF_NAMES, dirs))
     assert abs(fd - an) <= 1e-5 * max(1.0, abs(an)), (fd, an)
+
+
+@pytest.mark.parametrize("name,chunks", [("c2_J6", 0), ("c2_J6", 37), ("sho4_J8", 1), ("sho4_J8", 9), ("sum4", 5)])
+def test_factor_rev_accumulate_flag(env, name, chunks):
+    """C2B_ACCUMULATE: bt, bc, bU are added to (lane-group and generic kernels, chunked and not); ba, bV overwritten."""
+    ops, T, H, torch = env
+    import oracle
+    from celerite2_b200 import workloads as wl
+
+    P = oracle.port()
+    N = 1500
+    t, y, diag = wl.light_curve(N, 23)
+    c, a, U, V = P.get_celerite_matrices(*ALL_KERNELS[name], t, diag)
+    J = U.shape[1]
+    _, d_r, W_r, S_r = P.factor(t, c, a, U, V)
+    rng = np.random.default_rng(5)
+    bd, bW = rng.standard_normal(N), rng.standard_normal((N, J))
+    want = P.factor_rev(t, c, a, U, V, d_r, W_r, S_r, bd, bW)
+    pre = [rng.standard_normal(N), rng.standard_normal(J), rng.standard_normal((N, J))]
+    acc = [T(v) for v in pre]
+    ops.set_chunks_per_series(chunks)
+    bt, bc, ba, bU, bV = ops.factor_rev(T(t), T(c), T(a), T(U), T(V), T(d_r), T(W_r), T(S_r), T(bd), T(bW), accumulate_into=acc)
+    ops.set_chunks_per_series(0)
+    assert bt is acc[0] and bc is acc[1] and bU is acc[2]
+    assert relerr(H(bt), want[0] + pre[0]) < TOL
+    assert relerr(H(bc), want[1] + pre[1]) < TOL
+    assert relerr(H(ba), want[2]) < TOL
+    assert relerr(H(bU), want[3] + pre[2]) < TOL
+    assert relerr(H(bV), want[4]) < TOL
