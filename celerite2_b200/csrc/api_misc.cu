@@ -303,7 +303,10 @@ int c2b_get_celerite_matrices(int32_t layout, int64_t N, int32_t Jr, int32_t Jc,
   g.co_r_bs = (flags & C2B_SHARED_C) ? 0 : Jr;
   g.co_c_bs = (flags & C2B_SHARED_C) ? 0 : Jc;
   const int64_t total = batch * N;
-  C2B_LAUNCH("assemble_kernel", (cudaStream_t)stream_, assemble_kernel<<<(unsigned)((total + 127) / 128), 128, 0, (cudaStream_t)stream_>>>(g));
+  const size_t smem = (size_t)2 * kAsmThreads * (Jr + 2 * Jc) * sizeof(double);
+  if (smem > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+  C2B_LAUNCH("assemble_kernel", (cudaStream_t)stream_,
+             assemble_kernel<<<(unsigned)((total + kAsmThreads - 1) / kAsmThreads), kAsmThreads, smem, (cudaStream_t)stream_>>>(g));
   return C2B_OK;
 }
 

@@ -19,39 +19,57 @@ struct AsmArgs {
 C2B_DEV int col_cos(int layout, int Jr, int Jc, int j) { return layout ? Jr + 2 * j : Jr + j; }
 C2B_DEV int col_sin(int layout, int Jr, int Jc, int j) { return layout ? Jr + 2 * j + 1 : Jr + Jc + j; }
 
-__global__ void assemble_kernel(AsmArgs g) {
-  const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int J       = g.Jr + 2 * g.Jc;
-  if (gid >= g.batch * g.N) return;
-  const int64_t b = gid / g.N, n = gid % g.N;
-  const double *ar = g.ar + b * g.co_r_bs, *cr = g.cr + b * g.co_r_bs;
-  const double *ac = g.ac + b * g.co_c_bs, *bc = g.bc + b * g.co_c_bs, *cc = g.cc + b * g.co_c_bs, *dc = g.dc + b * g.co_c_bs;
-  double sum = 0.0;
-  for (int j = 0; j < g.Jr; ++j) sum += ar[j];
-  for (int j = 0; j < g.Jc; ++j) sum += ac[j];
-  const double xn = g.x[b * g.x_bs + n];
-  g.a_out[gid]    = g.diag[gid] + sum;
-  double *U = g.U_out + gid * J, *V = g.V_out + gid * J;
-  for (int j = 0; j < g.Jr; ++j) {
-    V[j] = 1.0;
-    U[j] = ar[j];
-  }
-  for (int j = 0; j < g.Jc; ++j) {
-    const int ic = col_cos(g.layout, g.Jr, g.Jc, j), is = col_sin(g.layout, g.Jr, g.Jc, j);
-    double sn, cs;
-    sincos(dc[j] * xn, &sn, &cs);
-    V[ic] = cs;
-    V[is] = sn;
-    U[ic] = ac[j] * cs + bc[j] * sn;
-    U[is] = ac[j] * sn - bc[j] * cs;
-  }
-  if (n == 0 && g.c_out) {
-    double *c = g.c_out + b * J;
-    for (int j = 0; j < g.Jr; ++j) c[j] = cr[j];
-    for (int j = 0; j < g.Jc; ++j) {
-      c[col_cos(g.layout, g.Jr, g.Jc, j)] = cc[j];
-      c[col_sin(g.layout, g.Jr, g.Jc, j)] = cc[j];
+// One thread per (series, row) computes the row; the CTA's 128 rows of U and V (contiguous in global memory, rows
+// being 8 J bytes) go through shared memory so that the stores are coalesced: thread-per-row stores have a stride
+// of 8 J bytes and write every 32-byte sector in pieces (r01e: 0.056 ms for 120 MB).
+constexpr int kAsmThreads = 128;
+
+__global__ void __launch_bounds__(kAsmThreads) assemble_kernel(AsmArgs g) {
+  extern __shared__ double asm_tile[];  // U rows [kAsmThreads * J], then V rows
+  const int64_t gid0 = (int64_t)blockIdx.x * kAsmThreads;
+  const int64_t gid  = gid0 + threadIdx.x;
+  const int J        = g.Jr + 2 * g.Jc;
+  const int64_t tot  = g.batch * g.N;
+  double *sU = asm_tile + (size_t)threadIdx.x * J, *sV = asm_tile + (size_t)kAsmThreads * J + (size_t)threadIdx.x * J;
+  if (gid < tot) {
+    const int64_t b = gid / g.N, n = gid % g.N;
+    const double *ar = g.ar + b * g.co_r_bs, *cr = g.cr + b * g.co_r_bs;
+    const double *ac = g.ac + b * g.co_c_bs, *bc = g.bc + b * g.co_c_bs, *cc = g.cc + b * g.co_c_bs, *dc = g.dc + b * g.co_c_bs;
+    double sum = 0.0;
+    for (int j = 0; j < g.Jr; ++j) sum += ar[j];
+    for (int j = 0; j < g.Jc; ++j) sum += ac[j];
+    const double xn = g.x[b * g.x_bs + n];
+    g.a_out[gid]    = g.diag[gid] + sum;
+    for (int j = 0; j < g.Jr; ++j) {
+      sV[j] = 1.0;
+      sU[j] = ar[j];
     }
+    for (int j = 0; j < g.Jc; ++j) {
+      const int ic = col_cos(g.layout, g.Jr, g.Jc, j), is = col_sin(g.layout, g.Jr, g.Jc, j);
+      double sn, cs;
+      sincos(dc[j] * xn, &sn, &cs);
+      sV[ic] = cs;
+      sV[is] = sn;
+      sU[ic] = ac[j] * cs + bc[j] * sn;
+      sU[is] = ac[j] * sn - bc[j] * cs;
+    }
+    if (n == 0 && g.c_out) {
+      double *c = g.c_out + b * J;
+      for (int j = 0; j < g.Jr; ++j) c[j] = cr[j];
+      for (int j = 0; j < g.Jc; ++j) {
+        c[col_cos(g.layout, g.Jr, g.Jc, j)] = cc[j];
+        c[col_sin(g.layout, g.Jr, g.Jc, j)] = cc[j];
+      }
+    }
+  }
+  __syncthreads();
+  const int64_t rows = tot - gid0 < kAsmThreads ? tot - gid0 : kAsmThreads;
+  const int cnt      = (int)rows * J;
+  double *U = g.U_out + gid0 * J, *V = g.V_out + gid0 * J;
+  const double *tU = asm_tile, *tV = asm_tile + (size_t)kAsmThreads * J;
+  for (int e = threadIdx.x; e < cnt; e += kAsmThreads) {
+    U[e] = tU[e];
+    V[e] = tV[e];
   }
 }
 
