@@ -223,29 +223,13 @@ def run_ours(args):
     def step_resident():
         return gp.log_likelihood_and_grad(co_d, t_d, y_d, d_d)
 
-    # staging buffers of the end-to-end path
-    t_s, y_s, d_s = torch.empty_like(t_d), torch.empty_like(y_d), torch.empty_like(d_d)
-    co_s = [torch.empty_like(v) for v in co_d]
-    n_out = 1 + sum(v.numel() for v in co_d)
-    out_h = torch.empty(n_out, dtype=torch.float64).pin_memory()
-    out_d = torch.empty(n_out, dtype=torch.float64, device=dev)
+    # end-to-end path: the host-buffer entry point (pinned host arrays in, pinned host result out)
+    host_api = gp.HostLogLikelihood(N, [v.shape for v in co_h], dev)
+    n_out = host_api.n_out
 
     def step_e2e():
-        t_s.copy_(t_h, non_blocking=True)
-        y_s.copy_(y_h, non_blocking=True)
-        d_s.copy_(d_h, non_blocking=True)
-        for s, h in zip(co_s, co_h):
-            s.copy_(h, non_blocking=True)
-        r = gp.log_likelihood_and_grad(co_s, t_s, y_s, d_s)
-        out_d[0:1].copy_(r["loglike"].reshape(1))
-        o = 1
-        for nm in gp.COEFF_NAMES:
-            g = r["grads"][nm]
-            out_d[o:o + g.numel()].copy_(g.reshape(-1))
-            o += g.numel()
-        out_h.copy_(out_d, non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the caller needs the value before the next step
-        return out_h
+        out, _ = host_api(co_h, t_h, y_h, d_h)
+        return out
 
     def barrier():
         if world > 1:

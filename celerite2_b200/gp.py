@@ -32,13 +32,15 @@ def log_likelihood(coeffs, t, y, diag, layout="blocked"):
     return ll, status
 
 
-def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grads=False):
-    """-> dict(loglike, status, grads = {ar, cr, ac, bc, cc, dc} [, t, y, diag])."""
+def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grads=False, y_ready=None):
+    """-> dict(loglike, status, grads = {ar, cr, ac, bc, cc, dc} [, t, y, diag]).
+    y_ready: optional CUDA event after which y is valid (y is first read by solve_lower, so its upload can overlap the
+    assembly and the factorisation; see HostLogLikelihood)."""
     c, a, U, V = ops.get_celerite_matrices(*coeffs, t, diag, layout=layout)
     d, W, S, status = ops.factor(t, c, a, U, V)
+    if y_ready is not None:
+        torch.cuda.current_stream().wait_event(y_ready)
     Y = y.unsqueeze(-1)
-    if Y.dim() < U.dim():  # shared y over a batch of coefficient sets
-        pass
     Z, F = ops.solve_lower(t, c, U, W, Y, workspace=True)
     out, bz, bd = ops.norm_logdet(d, Z.squeeze(-1), want_grad=True)
     N = diag.shape[-1]
@@ -50,3 +52,50 @@ def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grad
     if want_data_grads:
         res["grads"].update(t=g[6], y=bY.squeeze(-1), diag=g[7])
     return res
+
+
+class HostLogLikelihood:
+    """Host-buffer entry point: like the reference's GaussianProcess.compute + log_likelihood (core.py:262-317,407-428),
+    which take host arrays, this takes HOST tensors (pinned for speed) of one series, uploads them, runs the device
+    pipeline and returns the log-likelihood and the coefficient gradients in a pinned host buffer
+    [loglike | d/d ar | d/d cr | d/d ac | d/d bc | d/d cc | d/d dc].
+
+    t and diag are uploaded on the caller's stream; y goes up on a second stream and the pipeline waits for it only
+    where y is first read (solve_lower), so its transfer overlaps the assembly and the factorisation.
+    """
+
+    def __init__(self, N, coeff_shapes, device):
+        self.dev = device
+        f8 = dict(dtype=torch.float64, device=device)
+        self.t, self.y, self.diag = (torch.empty(N, **f8) for _ in range(3))
+        self.co = [torch.empty(tuple(sh), **f8) for sh in coeff_shapes]
+        self.n_out = 1 + sum(v.numel() for v in self.co)
+        self.out_d = torch.empty(self.n_out, **f8)
+        self.out_h = torch.empty(self.n_out, dtype=torch.float64).pin_memory()
+        self.side = torch.cuda.Stream(device=device)
+        self.y_ready = torch.cuda.Event()
+        self.h2d_bytes = 8 * (3 * N + sum(v.numel() for v in self.co))
+        self.d2h_bytes = 8 * self.n_out
+
+    def __call__(self, coeffs_h, t_h, y_h, diag_h):
+        main = torch.cuda.current_stream()
+        for s, h in zip(self.co, coeffs_h):
+            s.copy_(h, non_blocking=True)
+        self.t.copy_(t_h, non_blocking=True)
+        self.diag.copy_(diag_h, non_blocking=True)
+        # y follows t and diag over the link (it would only share their bandwidth if started with them) and overlaps
+        # the kernels that do not read it; waiting on `main` also orders it after the previous call's readers of y
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side):
+            self.y.copy_(y_h, non_blocking=True)
+            self.y_ready.record(self.side)
+        r = log_likelihood_and_grad(self.co, self.t, self.y, self.diag, y_ready=self.y_ready)
+        self.out_d[0:1].copy_(r["loglike"].reshape(1))
+        o = 1
+        for nm in COEFF_NAMES:
+            g = r["grads"][nm]
+            self.out_d[o:o + g.numel()].copy_(g.reshape(-1))
+            o += g.numel()
+        self.out_h.copy_(self.out_d, non_blocking=True)
+        main.synchronize()  # the caller needs the values
+        return self.out_h, r["status"]

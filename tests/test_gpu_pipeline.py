@@ -90,3 +90,29 @@ def test_batched_pipeline_shared_data():
         ll = _oracle_loglike(cb, t, y, diag)
         assert abs(float(r["loglike"][b].item()) - ll) <= 1e-10 * abs(ll)
     assert relerr(r["grads"]["ac"].shape, (B, 2)) == 0.0
+
+
+def test_host_buffer_entry_point_matches_device_pipeline():
+    """HostLogLikelihood (pinned host arrays in, y uploaded on a second stream) == the device-resident pipeline, on
+    repeated calls with changing data (the staging buffers are reused)."""
+    import torch
+
+    from celerite2_b200 import gp
+    from celerite2_b200 import workloads as wl
+
+    dev = torch.device("cuda:0")
+    co = [np.array(v, dtype=np.float64) for v in ALL_KERNELS["c2_J6"]]
+    N = 50000
+    co_h = [torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for v in co]
+    api = gp.HostLogLikelihood(N, [v.shape for v in co_h], dev)
+    for seed in (1, 2, 3):
+        t, y, diag = wl.light_curve(N, seed)
+        hs = [torch.from_numpy(v).pin_memory() for v in (t, y, diag)]
+        out, status = api(co_h, *hs)
+        assert int(status.item()) == 0
+        got = out.numpy().copy()
+        r = gp.log_likelihood_and_grad([v.to(dev) for v in co_h], *[v.to(dev) for v in hs])
+        want = np.concatenate([r["loglike"].reshape(1).cpu().numpy()] + [r["grads"][nm].reshape(-1).cpu().numpy() for nm in gp.COEFF_NAMES])
+        assert got.shape == want.shape
+        assert np.max(np.abs(got - want) / np.maximum(1.0, np.abs(want))) < 1e-12
+        assert abs(got[0] - _oracle_loglike(co, t, y, diag)) < 1e-10 * abs(got[0])
