@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
   __shared__ __align__(16) double stile[GP * GS];
   __shared__ __align__(16) double sprop[GP * R * JE];
   __shared__ __align__(16) double sxch[GP * 2 * JE];
+  __shared__ double scc[GP * JE];
   __shared__ __align__(16) double srows[GP * SS];  // the tile's S rows, flushed with wide stores once per tile
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
@@ -51,6 +52,10 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
   const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
   const double cc  = act ? (g.c + b * g.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
   double Sg[J];  // column c of Sigma: Sg[j] = Sigma(j, c)
 #pragma unroll
   for (int j = 0; j < J; ++j) Sg[j] = 0.0;
@@ -83,10 +88,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
     const int64_t nt = n0 + (int64_t)k * R;
-    if (c < J) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) pb[r * JE + c] = exp(cc * (tb[oT + r] - tb[oT + r + 1]));  // dt = 0 at n = 0
-    }
+    pairs.template eval<R, JE>(pb, c, cc, [&](int r) { return tb[oT + r] - tb[oT + r + 1]; });  // dt = 0 at n = 0
     __syncwarp();
     int stored = 0;  // S rows of this tile that are to be written
 #pragma unroll
@@ -164,6 +166,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_summary_kernel(Facto
   __shared__ __align__(16) double stile[GP * GS];
   __shared__ __align__(16) double sprop[GP * R * JE];
   __shared__ __align__(16) double sxch[GP * 4 * JE];
+  __shared__ double scc[GP * JE];
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
   const int64_t unit   = (int64_t)blockIdx.x * GP + gin;
@@ -180,6 +183,10 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_summary_kernel(Facto
   const GCopy<G> cp{c};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const double cc = act ? (g.c + b * g.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
   double A[J], Cm[J], Q[J];  // column c
 #pragma unroll
   for (int j = 0; j < J; ++j) {
@@ -209,10 +216,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_summary_kernel(Facto
     __syncwarp();
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
-    if (c < J) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) pb[r * JE + c] = exp(cc * (tb[oT + r] - tb[oT + r + 1]));  // dt = 0 at n = 0
-    }
+    pairs.template eval<R, JE>(pb, c, cc, [&](int r) { return tb[oT + r] - tb[oT + r + 1]; });  // dt = 0 at n = 0
     __syncwarp();
 #pragma unroll
     for (int r = 0; r < R; ++r) {

@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
   __shared__ __align__(16) double stile[GP * GS];
   __shared__ __align__(16) double sprop[GP * R * JE];
   __shared__ __align__(16) double sxch[GP * 2 * JE];
+  __shared__ double scc[GP * JE];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -47,6 +48,10 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
   const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(bW)) & 15) == 0);
   const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
   const double cc  = act ? (g.c + b * g.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
   double Gc[J];  // column c of G: Gc[j] = G(j, c)
   double Mr[J];  // summary: row c of M
 #pragma unroll
@@ -89,13 +94,8 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
     const int64_t nt = n1 - 1 - (int64_t)k * R;  // first row of the tile in visiting order
-    if (c < J) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int s    = R - 1 - r;
-        pb[r * JE + c] = exp(cc * (tb[oT + s] - tb[oT + s + 1]));  // dt = t_{n-1} - t_n, 0 at n = 0
-      }
-    }
+    // dt = t_{n-1} - t_n, 0 at n = 0
+    pairs.template eval<R, JE>(pb, c, cc, [&](int r) { return tb[oT + R - 1 - r] - tb[oT + R - r]; });
     __syncwarp();
 #pragma unroll
     for (int r = 0; r < R; ++r) {

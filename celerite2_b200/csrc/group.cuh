@@ -200,6 +200,74 @@ struct GTileStride {
   static constexpr int value = NBUF * TB + ((G % 16) - (NBUF * TB) % 16 + 16) % 16;
 };
 
+// Propagators exp(c_j dt) of a tile: pb[r * JE + j] for the R steps r of the tile and the J decay rates.  The exp is
+// half of a summary pass (r01g profile).  A complex term contributes two columns with the same decay rate
+// (terms.hpp:125; adjacent in the interleaved layout, Jc apart in the blocked one): two lanes that share their rate with
+// nobody else split the rows of the tile between them and each stores its results for both, which halves the exp
+// work of all-complex kernels (SHO, rotation, Matern terms).  Unpaired lanes evaluate all R rows.
+template <int J>
+struct PropPairs {
+  int mate;     // the lane that shares my decay rate, or -1
+  bool second;  // of a pair, I take the second half of the rows
+  // csm: the J decay rates of my group in shared memory, visible to all its lanes
+  C2B_DEV void init(const double *csm, int c) {
+    mate    = -1;
+    int cnt = 0;
+    if (c < J) {
+#pragma unroll
+      for (int j = 0; j < J; ++j)
+        if (j != c && csm[j] == csm[c]) {
+          mate = j;
+          ++cnt;
+        }
+    }
+    if (cnt != 1) mate = -1;
+    if (c >= J) mate = c;  // lanes without a column: nothing to evaluate, must not pull the warp into the unpaired path
+    second = mate >= 0 && c > mate;
+  }
+  // dt(r): time difference of step r (any lane may ask for any step).  No barriers inside.
+  template <int R, int JE, class DT>
+  C2B_DEV void eval(double *pb, int c, double cc, DT dt) const {
+    static_assert(R % 2 == 0, "tiles have an even number of rows");
+    if (c >= J) return;
+    const int r0 = second ? R / 2 : 0;
+#pragma unroll
+    for (int q = 0; q < R / 2; ++q) {
+      const int r    = r0 + q;
+      const double v = exp(cc * dt(r));
+      pb[r * JE + c] = v;
+      if (mate >= 0) pb[r * JE + mate] = v;
+    }
+    if (mate < 0) {
+#pragma unroll
+      for (int q = R / 2; q < R; ++q) pb[q * JE + c] = exp(cc * dt(q));
+    }
+  }
+};
+
+// Register version for the kernels where lane c only needs its own propagators: p[r], r < R.  A pair computes half
+// of the tile each and swaps halves with shuffles (all 32 lanes must call).
+template <int J, int G, int R, class DT>
+C2B_DEV void eval_props_reg(const PropPairs<J> &pr, int c, double cc, DT dt, double *p) {
+  static_assert(R % 2 == 0, "tiles have an even number of rows");
+  const int r0 = pr.second ? R / 2 : 0;
+  double mine[R / 2], other[R / 2];
+#pragma unroll
+  for (int q = 0; q < R / 2; ++q) mine[q] = exp(cc * dt(r0 + q));
+  const int src = pr.mate >= 0 ? pr.mate : c;  // lane within the group
+#pragma unroll
+  for (int q = 0; q < R / 2; ++q) other[q] = __shfl_sync(0xffffffffu, mine[q], src, G);
+  if (pr.mate < 0) {
+#pragma unroll
+    for (int q = 0; q < R / 2; ++q) other[q] = exp(cc * dt(R / 2 + q));
+  }
+#pragma unroll
+  for (int q = 0; q < R / 2; ++q) {
+    p[q]         = pr.second ? other[q] : mine[q];
+    p[R / 2 + q] = pr.second ? mine[q] : other[q];
+  }
+}
+
 // J consecutive doubles from 16-byte aligned shared memory
 template <int J>
 C2B_DEV void lds_row(const double *p, double *out) {

@@ -22,7 +22,9 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
   constexpr int TB  = (oZ + (SOLVE ? 0 : R) + 1) & ~1;
   constexpr int GS  = GTileStride<G, TB, 2>::value;
   constexpr int dir = LOWER ? 1 : -1;
+  constexpr int JE  = (J + 1) & ~1;
   __shared__ __align__(16) double stile[GP * GS];
+  __shared__ double scc[GP * JE];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -39,6 +41,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
   const GCopy<G> cp{c};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
   double Fc = 0.0;
   if (a.carry && act) {
     const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
@@ -70,14 +76,12 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
     __syncwarp();
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
-    // state-independent part of the whole tile first: R independent exp evaluations the compiler can interleave
+    // state-independent part of the whole tile first: independent exp evaluations the compiler can interleave
     double p[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const int s     = LOWER ? r : R - 1 - r;
-      const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
-      p[r]            = exp(cc * dt);
-    }
+    eval_props_reg<J, G, R>(pairs, c, cc, [&](int r) {
+      const int s = LOWER ? r : R - 1 - r;
+      return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+    }, p);
     double *Ft = F ? F + (nf + (int64_t)dir * k * R) * J + cj : nullptr;
     double *Zt = Z + (nf + (int64_t)dir * k * R);
 #pragma unroll
@@ -120,6 +124,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
   constexpr int GS = GTileStride<G, TB, 2>::value;
   __shared__ __align__(16) double stile[GP * GS];
   __shared__ __align__(16) double sprop[GP * R * JE];
+  __shared__ double scc[GP * JE];
   const int q         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -134,6 +139,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
   const GCopy<G> cp{q};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
+  PropPairs<J> pairs;
+  if (q < J) scc[gin * JE + q] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, q);
   double Gq[J];
 #pragma unroll
   for (int j = 0; j < J; ++j) Gq[j] = (j == q) ? 1.0 : 0.0;
@@ -160,14 +169,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
     __syncwarp();
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
-    if (q < J) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int s     = LOWER ? r : R - 1 - r;
-        const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
-        pb[r * JE + q]  = exp(cc * dt);
-      }
-    }
+    pairs.template eval<R, JE>(pb, q, cc, [&](int r) {
+      const int s = LOWER ? r : R - 1 - r;
+      return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+    });
     __syncwarp();
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -217,7 +222,9 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
   constexpr int GS  = GTileStride<G, TB, 2>::value;
   constexpr bool UP = !LOWER;  // the reverse of a lower sweep walks downwards
   constexpr int dir = UP ? 1 : -1;
+  constexpr int JE  = (J + 1) & ~1;
   __shared__ __align__(16) double stile[GP * GS];
+  __shared__ double scc[GP * JE];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -236,6 +243,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
   const GCopy<G> cp{c};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(F)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
   double bF = 0.0, bc_acc = 0.0, pend = 0.0;
   if (a.carry && act) {
     const int64_t leaf = LOWER ? a.C - 1 - chunk : chunk;
@@ -269,13 +280,11 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
     __syncwarp();
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
-    double p[R], dts[R];
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
+    double p[R];
+    eval_props_reg<J, G, R>(pairs, c, cc, [&](int r) {
       const int s = UP ? r : R - 1 - r;
-      dts[r]      = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
-      p[r]        = exp(cc * dts[r]);
-    }
+      return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+    }, p);
     const int64_t nt = nf + (int64_t)dir * k * R;  // first row of this tile in visiting order
     double *bAt = bA + nt * J + cj, *bBt = bB + nt * J + cj, *btt = bt + nt, *bYt = bY + nt;
 #pragma unroll
@@ -305,7 +314,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
       const double fac = gsum<G>(cc * bp);
       if (nb) {
         if (act) bAt[dir * J * r] = SOLVE ? -(bz * pf) : bz * pf;
-        bc_acc = fma(dts[r], bp, bc_acc);
+        bc_acc = fma(LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2], bp, bc_acc);
         if (c == 0) btt[dir * r] = pend - sgn * fac;
         pend = sgn * fac;
         bF   = p_c * nf_;
@@ -337,6 +346,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(S
   constexpr int dir = UP ? 1 : -1;
   __shared__ __align__(16) double stile[GP * GS];
   __shared__ __align__(16) double sprop[GP * R * JE];
+  __shared__ double scc[GP * JE];
   const int q         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
@@ -351,6 +361,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(S
   const GCopy<G> cp{q};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
+  PropPairs<J> pairs;
+  if (q < J) scc[gin * JE + q] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, q);
   double Gq[J];
 #pragma unroll
   for (int j = 0; j < J; ++j) Gq[j] = (j == q) ? 1.0 : 0.0;
@@ -379,14 +393,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(S
     __syncwarp();
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
-    if (q < J) {
-#pragma unroll
-      for (int r = 0; r < R; ++r) {
-        const int s     = UP ? r : R - 1 - r;
-        const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
-        pb[r * JE + q]  = exp(cc * dt);
-      }
-    }
+    pairs.template eval<R, JE>(pb, q, cc, [&](int r) {
+      const int s = UP ? r : R - 1 - r;
+      return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+    });
     __syncwarp();
     const int64_t nt = nf + (int64_t)dir * k * R;
 #pragma unroll
