@@ -97,6 +97,14 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
     // dt = t_{n-1} - t_n, 0 at n = 0
     pairs.template eval<R, JE>(pb, c, cc, [&](int r) { return tb[oT + R - 1 - r] - tb[oT + R - r]; });
     __syncwarp();
+    // also independent of the state: bW_n / d_n of the tile's rows (a division each, kept off the dependent chain)
+    double bwd[R], cbp[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s = R - 1 - r;
+      bwd[r]      = (act && r < rows) ? tb[oB + s * J + cj] / tb[oD + s] : 0.0;
+      cbp[r]      = 0.0;
+    }
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const int s     = R - 1 - r;
@@ -110,14 +118,12 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       if (WRITE) lds_row<J>(tb + s * J * J + J * cj, Sn);
       const double u_c  = act ? tb[oU + s * J + cj] : 0.0;
       const double w_c  = act ? tb[oW + s * J + cj] : 0.0;
-      const double bw_c = act ? tb[oB + s * J + cj] : 0.0;
       const double p_c  = act ? pb[r * JE + cj] : 1.0;
-      const double d_n  = live ? tb[oD + s] : 1.0;
       const double bd_n = tb[oE + s];
       double wG = 0.0;
 #pragma unroll
       for (int j = 0; j < J; ++j) wG = fma(w[j], Gc[j], wG);
-      const double bv_c = fma(2.0, wG, bw_c / d_n);
+      const double bv_c = fma(2.0, wG, bwd[r]);
       // ba_n = bd_n + w G w^T - w . bV_n   (reverse.hpp:30-33), one reduction for both
       const double ban = bd_n + gsum<G>(w_c * (wG - bv_c));
       const double y_c = fma(ban, u_c, bv_c);
@@ -156,10 +162,17 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
         for (int j = 0; j < J; ++j) Gc[j] *= p[j] * p_c;
       }
       if (WRITE) {
-        const double fac = gsum<G>(cc * bp);  // bp = 0 on rows without a predecessor
-        if (live) {
-          if (act) out_store(bU + n * J + c, nb ? -(xs * p_c) : 0.0, g.acc);
-          if (c == 0) out_store(bt + n, pend - fac, g.acc);
+        cbp[r] = cc * bp;  // bp = 0 on rows without a predecessor
+        if (live && act) out_store(bU + n * J + c, nb ? -(xs * p_c) : 0.0, g.acc);
+      }
+    }
+    if (WRITE) {
+      // bt_n = (term handed down by row n+1) - c . bp_n: the tile's R reductions at once, off the dependent chain
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const double fac = gsum<G>(cbp[r]);
+        if (r < rows) {
+          if (c == 0) out_store(bt + (nt - r), pend - fac, g.acc);
           pend = fac;
         }
       }

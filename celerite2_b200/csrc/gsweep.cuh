@@ -286,6 +286,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
       return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
     }, p);
     const int64_t nt = nf + (int64_t)dir * k * R;  // first row of this tile in visiting order
+    double cbp[R];
     double *bAt = bA + nt * J + cj, *bBt = bB + nt * J + cj, *btt = bt + nt, *bYt = bY + nt;
 #pragma unroll
     for (int r = 0; r < R; ++r) {
@@ -311,17 +312,22 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
       const double nf_ = SOLVE ? bF - au : bF + au;
       const double pf  = p_c * Fn;
       const double bp  = nb ? Fn * nf_ * p_c : 0.0;
-      const double fac = gsum<G>(cc * bp);
+      cbp[r]           = cc * bp;
       if (nb) {
         if (act) bAt[dir * J * r] = SOLVE ? -(bz * pf) : bz * pf;
         bc_acc = fma(LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2], bp, bc_acc);
-        if (c == 0) btt[dir * r] = pend - sgn * fac;
-        pend = sgn * fac;
-        bF   = p_c * nf_;
+        bF     = p_c * nf_;
       } else if (live) {
         if (act) bAt[dir * J * r] = 0.0;
-        if (c == 0) btt[dir * r] = pend;
-        pend = 0.0;
+      }
+    }
+    // bt_n = (term handed over by the previous row) -/+ c . bp_n: the tile's R reductions at once, off the dependent chain
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const double fac = gsum<G>(cbp[r]);  // 0 on rows without a predecessor
+      if (r < rows) {
+        if (c == 0) btt[dir * r] = pend - sgn * fac;
+        pend = sgn * fac;
       }
     }
     __syncwarp();
