@@ -129,6 +129,11 @@ struct AffV {
   static constexpr int MJ = Width<JT>::MAXJ;
   __host__ __device__ static int esize(int J, int K) { return J * J + J * K; }
   __host__ __device__ static int ssize(int J, int K) { return J * K; }
+  // element = head (shared by all right-hand sides) + ecol doubles per column; state = shead + scol per column
+  __host__ __device__ static int ehead(int J) { return J * J; }
+  __host__ __device__ static int ecol(int J) { return J; }
+  __host__ __device__ static int shead(int) { return 0; }
+  __host__ __device__ static int scol(int J) { return J; }
   C2B_DEV static void combine(int J, int K, const double *e1, const double *e2, double *out) {
     double M1[MJ * MJ], M2[MJ * MJ], M[MJ * MJ];
     for (int i = 0; i < J * J; ++i) {
@@ -179,6 +184,10 @@ struct DiagV {
   static constexpr int kJT    = JT;
   __host__ __device__ static int esize(int J, int K) { return J + J * K; }
   __host__ __device__ static int ssize(int J, int K) { return J * K; }
+  __host__ __device__ static int ehead(int J) { return J; }
+  __host__ __device__ static int ecol(int J) { return J; }
+  __host__ __device__ static int shead(int) { return 0; }
+  __host__ __device__ static int scol(int J) { return J; }
   C2B_DEV static void combine(int J, int K, const double *e1, const double *e2, double *out) {
     for (int j = 0; j < J; ++j) out[j] = e2[j] * e1[j];
     for (int k = 0; k < K; ++k)
@@ -200,6 +209,10 @@ struct Cong {
   static constexpr int MJ = Width<JT>::MAXJ;
   __host__ __device__ static int esize(int J, int) { return 2 * J * J; }
   __host__ __device__ static int ssize(int J, int) { return J * J; }
+  __host__ __device__ static int ehead(int J) { return 2 * J * J; }
+  __host__ __device__ static int ecol(int) { return 0; }
+  __host__ __device__ static int shead(int J) { return J * J; }
+  __host__ __device__ static int scol(int) { return 0; }
   C2B_DEV static void sandwich(int J, const double *M, const double *G, const double *B, double *out) {
     double T[MJ * MJ], R[MJ * MJ];
     mm<JT>(J, G, M, T);    // G M
@@ -255,6 +268,10 @@ struct Lft {
   static constexpr int MJ = Width<JT>::MAXJ;
   __host__ __device__ static int esize(int J, int) { return 3 * J * J; }
   __host__ __device__ static int ssize(int J, int) { return J * J; }
+  __host__ __device__ static int ehead(int J) { return 3 * J * J; }
+  __host__ __device__ static int ecol(int) { return 0; }
+  __host__ __device__ static int shead(int J) { return J * J; }
+  __host__ __device__ static int scol(int) { return 0; }
   C2B_DEV static void combine(int J, int, const double *e1, const double *e2, double *out) {
     const int JJ = J * J;
     double Mx[MJ * MJ], R[2 * MJ * MJ], T[MJ * MJ], T2[MJ * MJ], A2[MJ * MJ];

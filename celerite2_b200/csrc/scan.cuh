@@ -218,55 +218,69 @@ C2B_DEV void block_down(const BlockTree &bt, int J, int K, int es, int ss, const
 
 constexpr int kCoopThreadsMax = 512;
 
+// Elements of the multi-right-hand-side sweeps are a J x J head plus J doubles per column, and with many columns a
+// whole element no longer fits a block-resident tree.  The columns do not interact, so the scan is cut into slices
+// of kb columns (blockIdx.y): every slice keeps [head | its columns] in shared memory, recomputes the (cheap) head
+// products, and only slice 0 writes the heads back.
+// n local elements of `loc` doubles  <->  global elements of `glob` doubles: [0, head) maps to [0, head), the rest
+// to goff + (r - head)
+C2B_DEV void slice_in(double *dst, const double *src, int n, int loc, int glob, int head, int goff) {
+  for (int e = threadIdx.x; e < n * loc; e += blockDim.x) {
+    const int i = e / loc, r = e - i * loc;
+    dst[e]      = src[(size_t)i * glob + (r < head ? r : r - head + goff)];
+  }
+}
+C2B_DEV void slice_out(double *dst, const double *src, int n, int loc, int glob, int head, int goff, bool with_head) {
+  for (int e = threadIdx.x; e < n * loc; e += blockDim.x) {
+    const int i = e / loc, r = e - i * loc;
+    if (r >= head || with_head) dst[(size_t)i * glob + (r < head ? r : r - head + goff)] = src[e];
+  }
+}
+
 // DIR: 0 = up only, 1 = down only, 2 = up then down (the launch that contains the top of the tree)
 template <class Mon, int DIR>
-__global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int64_t batch, Levels lv, int lb, int nlev, double *nodes_all,
-                                                             double *states_all, const double *init) {
+__global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int kb, int64_t batch, Levels lv, int lb, int nlev,
+                                                             double *nodes_all, double *states_all, const double *init) {
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double sm_all[];
-  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
-  const int wsm    = Coop<Mon>::wsmem(J, K);
+  const int k0  = blockIdx.y * kb;                       // my columns: [k0, k0 + kl)
+  const int kl  = K - k0 < kb ? K - k0 : kb;
+  const int esg = Mon::esize(J, K), ssg = Mon::ssize(J, K);   // global element / state
+  const int es = Mon::esize(J, kl), ss = Mon::ssize(J, kl);   // local (my slice)
+  const int eh = Mon::ehead(J), sh = Mon::shead(J);
+  const int ego = eh + Mon::ecol(J) * k0, sgo = sh + Mon::scol(J) * k0;
+  const int wsm    = Coop<Mon>::wsmem(J, kl);
   const int nwarps = blockDim.x >> 5, wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const BlockTree bt = make_block_tree(lv, lb, nlev);
   const int slots    = 2 * bt.LB - 1;
   double *tree = sm_all;                                         // slots * es
   double *st   = tree + (size_t)slots * es;                      // slots * ss (DIR >= 1)
   double *sm   = st + (DIR >= 1 ? (size_t)slots * ss : 0) + (size_t)wib * wsm;
-  double *nodes  = nodes_all + bt.b * lv.total * es;
-  double *states = DIR >= 1 ? states_all + bt.b * lv.total * ss : nullptr;
+  double *nodes  = nodes_all + bt.b * lv.total * esg;
+  double *states = DIR >= 1 ? states_all + bt.b * lv.total * ssg : nullptr;
   // load: level lb nodes (up) / all present local levels below the top one (down)
   const int qload = DIR == 1 ? bt.nl - 1 : 0;
-  for (int q = 0; q <= qload; ++q) {
-    const double *src = nodes + (lv.off[lb + q] + ((bt.blk * bt.LB) >> q)) * es;
-    double *dst       = tree + (size_t)bt.off(q) * es;
-    const int n       = bt.cnt[q] * es;
-    for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = src[e];
-  }
-  if (DIR == 1) {
-    const double *src = states + (lv.off[lb + bt.nl] + ((bt.blk * bt.LB) >> bt.nl)) * ss;
-    double *dst       = st + (size_t)bt.off(bt.nl) * ss;
-    for (int e = threadIdx.x; e < bt.cnt[bt.nl] * ss; e += blockDim.x) dst[e] = src[e];
-  }
+  for (int q = 0; q <= qload; ++q)
+    slice_in(tree + (size_t)bt.off(q) * es, nodes + (lv.off[lb + q] + ((bt.blk * bt.LB) >> q)) * esg, bt.cnt[q], es, esg, eh, ego);
+  if (DIR == 1)
+    slice_in(st + (size_t)bt.off(bt.nl) * ss, states + (lv.off[lb + bt.nl] + ((bt.blk * bt.LB) >> bt.nl)) * ssg, bt.cnt[bt.nl], ss, ssg,
+             sh, sgo);
   __syncthreads();
   if (DIR != 1) {
-    block_up<Mon>(bt, J, K, es, tree, sm, wib, lane, nwarps);
-    for (int q = 1; q <= bt.nl; ++q) {
-      double *dst       = nodes + (lv.off[lb + q] + ((bt.blk * bt.LB) >> q)) * es;
-      const double *src = tree + (size_t)bt.off(q) * es;
-      const int n       = bt.cnt[q] * es;
-      for (int e = threadIdx.x; e < n; e += blockDim.x) dst[e] = src[e];
-    }
+    block_up<Mon>(bt, J, kl, es, tree, sm, wib, lane, nwarps);
+    for (int q = 1; q <= bt.nl; ++q)
+      slice_out(nodes + (lv.off[lb + q] + ((bt.blk * bt.LB) >> q)) * esg, tree + (size_t)bt.off(q) * es, bt.cnt[q], es, esg, eh, ego,
+                blockIdx.y == 0);
   }
   if (DIR == 2) {
     // this CTA holds the root: seed it
     double *dst = st + (size_t)bt.off(bt.nl) * ss;
-    for (int e = threadIdx.x; e < ss; e += blockDim.x) dst[e] = init ? init[bt.b * ss + e] : 0.0;
+    for (int e = threadIdx.x; e < ss; e += blockDim.x) dst[e] = init ? init[bt.b * ssg + (e < sh ? e : e - sh + sgo)] : 0.0;
     __syncthreads();
   }
   if (DIR >= 1) {
-    block_down<Mon>(bt, J, K, es, ss, tree, st, sm, wib, lane, nwarps);
-    double *dst = states + (lv.off[lb] + bt.blk * bt.LB) * ss;
-    for (int e = threadIdx.x; e < bt.cnt[0] * ss; e += blockDim.x) dst[e] = st[e];
+    block_down<Mon>(bt, J, kl, es, ss, tree, st, sm, wib, lane, nwarps);
+    slice_out(states + (lv.off[lb] + bt.blk * bt.LB) * ssg, st, bt.cnt[0], ss, ssg, sh, sgo, true);
   }
 }
 
@@ -285,23 +299,46 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop) {
-    const int es = Mon::esize(J, K), ss = Mon::ssize(J, K), wsm = Coop<Mon>::wsmem(J, K);
-    // levels per launch / warps per CTA: the largest configuration whose shared memory (sized for the launch that
-    // holds nodes and states) lets two CTAs share an SM
+    // levels per launch / warps per CTA / columns per slice: the largest configuration whose shared memory (sized
+    // for the launch that holds nodes and states) lets two CTAs share an SM
     static const int cand[][2] = {{5, 16}, {5, 8}, {4, 8}, {4, 4}, {3, 4}, {2, 2}, {1, 1}};
-    int nlev = 1, nwarps = 1;
+    const int eh = Mon::ehead(J) + Mon::shead(J), ec = Mon::ecol(J) + Mon::scol(J);
+    int nlev = 1, nwarps = 1, kb = K;
     size_t smem = 0;
-    for (auto &cd : cand) {
-      const size_t slots = (size_t)(2 << cd[0]) - 1;
-      smem               = (slots * (es + ss) + (size_t)cd[1] * wsm) * sizeof(double);
-      nlev               = cd[0];
-      nwarps             = cd[1];
-      if (smem <= 110 * 1024) break;
+    bool found = false;
+    // first choice: at least four levels per launch with two CTAs per SM; otherwise one CTA per SM
+    for (int pass = 0; pass < 2 && !found; ++pass) {
+      const long budget_bytes = pass == 0 ? 110 * 1024 : 200 * 1024;
+      for (auto &cd : cand) {
+        if (pass == 0 && cd[0] < 4) break;
+        const long slots  = (2L << cd[0]) - 1;
+        nlev              = cd[0];
+        nwarps            = cd[1];
+        const long budget = budget_bytes / (long)sizeof(double);
+        kb                = K;
+        if (ec > 0) {
+          // widest slice that fits: per-warp scratch is taken at the full width (an upper bound)
+          const long per_slot = (budget - (long)nwarps * Coop<Mon>::wsmem(J, K)) / slots;
+          long fit            = (per_slot - eh) / ec;
+          if (fit > K) fit = K;
+          kb = (int)fit;
+        }
+        const bool ok = ec > 0 ? kb >= (K < 4 ? K : 4) : true;
+        if (kb < 1) kb = 1;
+        const int nsl = (K + kb - 1) / kb;
+        kb            = (K + nsl - 1) / nsl;  // balanced slices
+        smem = ((size_t)slots * (Mon::esize(J, kb) + Mon::ssize(J, kb)) + (size_t)nwarps * Coop<Mon>::wsmem(J, kb)) * sizeof(double);
+        if (ok && smem <= (size_t)budget_bytes) {
+          found = true;
+          break;
+        }
+      }
     }
     if (smem > 220 * 1024) {
       set_error("scan: summary element too large for the block-resident tree (%zu bytes of shared memory)", smem);
       return C2B_ERR_INVALID_ARGUMENT;
     }
+    const unsigned nslices = (unsigned)((K + kb - 1) / kb);
     static bool attr_done[64] = {};  // per instantiation and device
     int dev = 0;
     C2B_CUDA(cudaGetDevice(&dev));
@@ -314,15 +351,15 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
     const int top = lv.nlev - 1;
     int bases[kMaxLevels], nb = 0;
     for (int lb = 0; lb < top || nb == 0; lb += nlev) bases[nb++] = lb;
-    auto grid_of = [&](int lb) { return (unsigned)(batch * ((lv.count[lb] + (1 << nlev) - 1) >> nlev)); };
+    auto grid_of = [&](int lb) { return dim3((unsigned)(batch * ((lv.count[lb] + (1 << nlev) - 1) >> nlev)), nslices); };
     for (int q = 0; q + 1 < nb; ++q)
       C2B_LAUNCH("scan_up_block", stream,
-                 (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, batch, lv, bases[q], nlev, nodes, states, init)));
+                 (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
     C2B_LAUNCH("scan_top_block", stream,
-               (scan_block<Mon, 2><<<grid_of(bases[nb - 1]), nwarps * 32, smem, stream>>>(J, K, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
+               (scan_block<Mon, 2><<<grid_of(bases[nb - 1]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
     for (int q = nb - 2; q >= 0; --q)
       C2B_LAUNCH("scan_down_block", stream,
-                 (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, batch, lv, bases[q], nlev, nodes, states, init)));
+                 (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
     return C2B_OK;
   } else {
   const int threads  = 128;  // 4 warps
