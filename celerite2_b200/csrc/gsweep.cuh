@@ -438,6 +438,161 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(S
 }
 
 // =================================================================================================================
+// Multi-right-hand-side solves (K > 1) on staged tiles: one CTA per (series, chunk); thread q owns column q and
+// carries its J-vector state in registers, so the columns never talk to each other.  The summary pass runs J + K
+// columns (J unit vectors -> transition M, then the K right-hand sides -> b), the apply pass K.  The chunk's rows
+// are staged in tiles of R rows shared by the whole CTA (A, B rows, time stamps, the tile of Y), the tile's
+// exp(c dt) are evaluated once per CTA, and every thread reads a row's A / B / propagator vectors as 16-byte
+// shared-memory broadcasts (the first version broadcast them with 6 J shuffles per row: c4 at 3.9 % of the roofline).
+// More columns than threads: the CTA walks the chunk once per group of kColThreads columns.
+// =================================================================================================================
+constexpr int kColThreads = 256;
+
+struct CtaCopy {
+  int c, n;  // my thread, threads in the CTA
+  C2B_DEV void run(double *dst, const double *src, int cnt, bool wide) const {
+    if (wide) {
+      for (int e = 2 * c; e < cnt; e += 2 * n) cp_async16(dst + e, src + e);
+    } else {
+      for (int e = c; e < cnt; e += n) cp_async8(dst + e, src + e);
+    }
+  }
+  C2B_DEV void run_t(double *dst, const double *t, int64_t first, int cnt, int64_t N) const {
+    for (int e = c; e < cnt; e += n) {
+      int64_t i = first + e;
+      i         = i < 0 ? 0 : (i > N - 1 ? N - 1 : i);
+      cp_async8(dst + e, t + i);
+    }
+  }
+};
+
+// dynamic shared memory: 2 x [A R*J | B R*J | t R+2 (+pad) | Y R*YW] then P R*J, c J
+template <int J>
+__host__ __device__ inline size_t csweep_smem_doubles(int yw) {
+  constexpr int R = kTileRows;
+  const int tb    = 2 * R * J + ((R + 2 + 1) & ~1) + R * yw;
+  return (size_t)2 * tb + R * J + J;
+}
+
+template <int J, bool LOWER, bool SUMMARY>
+__global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a) {
+  constexpr int R  = kTileRows;
+  constexpr int oB = R * J, oT = 2 * R * J, oY = oT + ((R + 2 + 1) & ~1);
+  extern __shared__ __align__(16) double cs_smem[];
+  const int NT         = blockDim.x;
+  const int tid        = threadIdx.x;
+  const int64_t chunk  = blockIdx.x % a.C, b = blockIdx.x / a.C;
+  const int64_t n0     = chunk * a.L;
+  const int64_t n1     = n0 + a.L < a.N ? n0 + a.L : a.N;
+  const int ncol       = SUMMARY ? J + a.K : a.K;
+  const int yw         = NT < a.K ? NT : a.K;  // widest slice of Y a column group can need
+  const int TB         = oY + R * yw;
+  double *pb           = cs_smem + 2 * TB;
+  double *csm          = pb + R * J;
+  const double *t      = a.t + b * a.t_bs;
+  const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J;
+  const double *Y = a.Y + b * a.y_bs;
+  double *Z = a.Z + b * a.N * (int64_t)a.K;
+  double *F = (!SUMMARY && a.F) ? a.F + b * a.N * (int64_t)J * a.K : nullptr;
+  const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
+  const CtaCopy cp{tid, NT};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
+  if (tid < J) csm[tid] = (a.c + b * a.c_bs)[tid];
+  const int cnt   = (int)(n1 - n0);
+  const int ntile = (cnt + R - 1) / R;
+  constexpr int dir = LOWER ? 1 : -1;
+  const int64_t nf  = LOWER ? n0 : n1 - 1;
+  for (int q0 = 0; q0 < ncol; q0 += NT) {
+    const int q      = q0 + tid;  // my column
+    const bool have  = q < ncol;
+    const bool basis = SUMMARY && q < J;
+    const int k      = SUMMARY ? q - J : q;  // real column index
+    // real columns of this group: [kc0, kc0 + kw)
+    const int kc0 = SUMMARY ? (q0 > J ? q0 - J : 0) : q0;
+    const int kc1 = SUMMARY ? (q0 + NT - J < a.K ? q0 + NT - J : a.K) : (q0 + NT < a.K ? q0 + NT : a.K);
+    const int kw  = kc1 > kc0 ? kc1 - kc0 : 0;
+    double Fk[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) Fk[j] = (basis && j == q) ? 1.0 : 0.0;
+    if (!SUMMARY && a.carry && have) {
+      const double *st = a.carry + (b * a.node_stride + leaf) * (int64_t)(J * a.K) + (int64_t)J * k;
+#pragma unroll
+      for (int j = 0; j < J; ++j) Fk[j] = st[j];
+    }
+    auto issue = [&](int kt) {
+      if (kt < ntile) {
+        const int rows   = cnt - kt * R < R ? cnt - kt * R : R;
+        const int64_t lo = LOWER ? n0 + (int64_t)kt * R : n1 - (int64_t)kt * R - rows;
+        const int pad    = LOWER ? 0 : R - rows;
+        double *tb       = cs_smem + (kt & 1) * TB;
+        cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+        cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
+        cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+        for (int r = 0; r < rows; ++r) cp.run(tb + oY + (pad + r) * yw, Y + (lo + r) * (int64_t)a.K + kc0, kw, false);
+      }
+      cp_async_commit();
+    };
+    __syncthreads();  // the previous column group is done with the buffers
+    issue(0);
+    issue(1);
+    for (int kt = 0; kt < ntile; ++kt) {
+      cp_async_wait<1>();
+      __syncthreads();
+      const double *tb = cs_smem + (kt & 1) * TB;
+      const int rows   = cnt - kt * R < R ? cnt - kt * R : R;
+      for (int i = tid; i < R * J; i += NT) {
+        const int r = i / J, j = i - r * J;
+        const int s = LOWER ? r : R - 1 - r;
+        const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+        pb[i] = exp(csm[j] * dt);  // dt = 0 (propagator 1) at the end of the series
+      }
+      __syncthreads();
+      const int64_t nt = nf + (int64_t)dir * kt * R;  // first row of the tile in visiting order
+      if (have) {
+#pragma unroll 2
+        for (int r = 0; r < R; ++r) {
+          if (r < rows) {
+            const int s     = LOWER ? r : R - 1 - r;
+            const int64_t n = nt + dir * r;
+            if (F) {
+#pragma unroll
+              for (int j = 0; j < J; ++j) F[n * (int64_t)J * a.K + (int64_t)J * k + j] = Fk[j];  // (j, k) at j + J*k
+            }
+            double p[J], av[J], bv[J];
+            lds_row<J>(pb + r * J, p);
+            lds_row<J>(tb + s * J, av);
+            double sm = 0.0;
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+              Fk[j] = p[j] * Fk[j];
+              sm    = fma(av[j], Fk[j], sm);
+            }
+            const double y = basis ? 0.0 : tb[oY + s * yw + (k - kc0)];
+            const double z = y - sm;
+            if (!SUMMARY) Z[n * (int64_t)a.K + k] = z;
+            lds_row<J>(tb + oB + s * J, bv);
+#pragma unroll
+            for (int j = 0; j < J; ++j) Fk[j] = fma(bv[j], z, Fk[j]);
+          }
+        }
+      }
+      __syncthreads();
+      issue(kt + 2);
+    }
+    if (SUMMARY && have) {
+      double *e = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J * J + J * a.K);
+      if (basis) {
+#pragma unroll
+        for (int j = 0; j < J; ++j) e[j * J + q] = Fk[j];
+      } else {
+#pragma unroll
+        for (int j = 0; j < J; ++j) e[J * J + j + J * k] = Fk[j];
+      }
+    }
+  }
+}
+
+// =================================================================================================================
 // Multi-right-hand-side solves (K > 1): one warp per (series, chunk, tile of 32 columns); lane k of the warp
 // carries the J-vector state of ITS column, so the columns never talk to each other.  The row's A / B entries and
 // exp(c dt) are fetched / evaluated once per row by lanes 0..J-1 and broadcast with shuffles.  Y and Z accesses

@@ -54,21 +54,28 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
   return C2B_OK;
 }
 
-// K > 1 solves with a compile-time width: one warp per 32 columns (csweep_kernel)
+// K > 1 solves with a compile-time width: one CTA per chunk, one thread per column (csweep_tile_kernel)
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   if constexpr (JT > 0 && SOLVE) {
+    auto threads_for = [](int ncol) {
+      int nt = (ncol + 31) / 32 * 32;
+      return nt > kColThreads ? kColThreads : nt;
+    };
+    const unsigned grid = (unsigned)(a.batch * a.C);
     if (a.C > 1) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
-      const int64_t warps = a.batch * a.C * ((JT + a.K + 31) / 32);
-      C2B_LAUNCH("csweep_summary_kernel", stream, csweep_kernel<JT, LOWER, true><<<(unsigned)((warps + 3) / 4), 128, 0, stream>>>(a));
+      const int nt  = threads_for(JT + a.K);
+      const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
+      C2B_LAUNCH("csweep_summary_kernel", stream, (csweep_tile_kernel<JT, LOWER, true><<<grid, nt, smem, stream>>>(a)));
       int rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
-    const int64_t warps = a.batch * a.C * ((a.K + 31) / 32);
-    C2B_LAUNCH("csweep_apply_kernel", stream, csweep_kernel<JT, LOWER, false><<<(unsigned)((warps + 3) / 4), 128, 0, stream>>>(a));
+    const int nt      = threads_for(a.K);
+    const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
+    C2B_LAUNCH("csweep_apply_kernel", stream, (csweep_tile_kernel<JT, LOWER, false><<<grid, nt, smem, stream>>>(a)));
   }
   return C2B_OK;
 }
