@@ -33,6 +33,22 @@ _SIGS = {
     "c2b_add_inplace": [_i64, _vp, _vp, _vp],
     "c2b_solve_lower_noalloc": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp],
 }
+
+
+class Segment(ctypes.Structure):
+    """c2b_segment_t (include/celerite2_b200.h)"""
+    _fields_ = [("phase", _i32), ("has_left", _i32), ("has_right", _i32), ("reserved", _i32),
+                ("state_in", _vp), ("summary_out", _vp), ("edge_out", _vp)]
+
+
+SEG_SUMMARISE, SEG_APPLY = 1, 2
+_segp = ctypes.POINTER(Segment)
+_SIGS["c2b_factor_segment"] = _SIGS["c2b_factor"] + [_segp]
+_SIGS["c2b_factor_rev_segment"] = _SIGS["c2b_factor_rev"] + [_segp]
+_SIGS["c2b_solve_lower_segment"] = [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp, _segp]
+_SIGS["c2b_solve_lower_rev_segment"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp, _segp]
+_SIGS["c2b_segment_sizes"] = [_i32, _i32, _i32, ctypes.POINTER(_i64), ctypes.POINTER(_i64)]
+_SIGS["c2b_segment_carry"] = [_i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp]
 for _op in ("solve_lower", "solve_upper", "matmul_lower", "matmul_upper"):
     _SIGS["c2b_" + _op] = [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp]
     _SIGS["c2b_" + _op + "_rev"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp]

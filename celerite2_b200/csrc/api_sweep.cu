@@ -5,7 +5,7 @@ namespace c2b {
 
 static int sizes_sweep(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb) {
   *pl = make_plan(N, batch, (K + 7) / 8, J);  // K columns already supply parallelism: fewer chunks per series
-  if (pl->C > 1) {
+  if (pl->C > 1 || batch == 1) {
     const int es = solve ? J * J + J * K : J + J * K;
     take_scan(ar, batch, pl->C, es, J * K, sb);
   }
@@ -23,7 +23,7 @@ size_t scratch_sweep(bool solve, int64_t N, int J, int K, int64_t batch) {
 static int sizes_sweep_rev(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb, double **bc_part,
                            double **bt_edge) {
   *pl = make_plan(N, batch, (K + 7) / 8, J);  // K columns already supply parallelism: fewer chunks per series
-  if (pl->C > 1) {
+  if (pl->C > 1 || batch == 1) {
     const int es = solve ? J * J + J * K : J + J * K;
     take_scan(ar, batch, pl->C, es, J * K, sb);
   }
@@ -42,13 +42,21 @@ size_t scratch_sweep_rev(bool solve, int64_t N, int J, int K, int64_t batch) {
 }
 
 
+int segment_setup(const c2b_segment_t *seg, int64_t N, int64_t batch, const void *scratch, bool reverse_op, Seg *out, int64_t *tmin,
+                  int64_t *tmax);  // api_factor.cu
+
 template <bool SOLVE, bool LOWER>
 static int sweep_entry(int64_t N, int J, int K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
-                       const double *Y, double *Z, double *F, int flags, void *scratch, size_t scratch_bytes, void *stream_) {
+                       const double *Y, double *Z, double *F, int flags, void *scratch, size_t scratch_bytes, void *stream_,
+                       const c2b_segment_t *seg = nullptr) {
   int rc = check_common(N, J, batch);
   if (rc) return rc;
   C2B_REQUIRE(K >= 1, "K (number of right-hand sides) must be >= 1");
   C2B_REQUIRE(t && c && U && W && Y && Z, "null data pointer");
+  Seg sg;
+  int64_t tmin, tmax;
+  rc = segment_setup(seg, N, batch, scratch, false, &sg, &tmin, &tmax);
+  if (rc) return rc;
   cudaStream_t stream = (cudaStream_t)stream_;
   Plan pl;
   ScanBuffers sb;
@@ -62,7 +70,7 @@ static int sweep_entry(int64_t N, int J, int K, int64_t batch, const double *t, 
     sizes_sweep(SOLVE, N, J, K, batch, &pl, ar, &sb);
     SweepArgs a;
     memset(&a, 0, sizeof(a));
-    a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.K = K;
+    a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.tmin = tmin; a.tmax = tmax; a.seg = sg; a.K = K;
     a.t = t; a.c = c; a.Y = Y; a.Z = Z; a.F = F;
     a.A = LOWER ? U : W;
     a.B = LOWER ? W : U;
@@ -81,11 +89,16 @@ static int sweep_entry(int64_t N, int J, int K, int64_t batch, const double *t, 
 template <bool SOLVE, bool LOWER>
 static int sweep_rev_entry(int64_t N, int J, int K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
                            const double *Y, const double *Z, const double *F, const double *bZ, double *bt, double *bc, double *bU,
-                           double *bW, double *bY, int flags, void *scratch, size_t scratch_bytes, void *stream_) {
+                           double *bW, double *bY, int flags, void *scratch, size_t scratch_bytes, void *stream_,
+                           const c2b_segment_t *seg = nullptr) {
   int rc = check_common(N, J, batch);
   if (rc) return rc;
   C2B_REQUIRE(K >= 1, "K (number of right-hand sides) must be >= 1");
   C2B_REQUIRE(t && c && U && W && Y && Z && F && bZ && bt && bc && bU && bW && bY, "null data pointer");
+  Seg sg;
+  int64_t tmin, tmax;
+  rc = segment_setup(seg, N, batch, scratch, true, &sg, &tmin, &tmax);
+  if (rc) return rc;
   cudaStream_t stream = (cudaStream_t)stream_;
   Plan pl;
   ScanBuffers sb;
@@ -99,7 +112,7 @@ static int sweep_rev_entry(int64_t N, int J, int K, int64_t batch, const double 
   sizes_sweep_rev(SOLVE, N, J, K, batch, &pl, ar, &sb, &bc_part, &bt_edge);
   SweepRevArgs a;
   memset(&a, 0, sizeof(a));
-  a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.K = K;
+  a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.tmin = tmin; a.tmax = tmax; a.seg = sg; a.K = K;
   a.t = t; a.c = c; a.Y = Y; a.Z = Z; a.F = F; a.bZ = bZ;
   a.A = LOWER ? U : W;
   a.B = LOWER ? W : U;
@@ -169,6 +182,29 @@ int c2b_matmul_upper_rev(int64_t N, int32_t J, int32_t K, int64_t batch, const d
   c2b::OpScope _op("c2b_matmul_upper_rev");
   return c2b::sweep_rev_entry<false, false>(N, J, K, batch, t, c, U, V, Y, Z, F, bZ, bt, bc, bU, bV, bY, flags, scratch, scratch_bytes,
                                             stream);
+}
+
+int c2b_solve_lower_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                            const double *W, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                            void *stream, const c2b_segment_t *seg) {
+  c2b::OpScope _op("c2b_solve_lower");
+  if (!seg) {
+    c2b::set_error("c2b_solve_lower_segment: seg is NULL");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  return c2b::sweep_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, F, flags, scratch, scratch_bytes, stream, seg);
+}
+int c2b_solve_lower_rev_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                                const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                                double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                                void *stream, const c2b_segment_t *seg) {
+  c2b::OpScope _op("c2b_solve_lower_rev");
+  if (!seg) {
+    c2b::set_error("c2b_solve_lower_rev_segment: seg is NULL");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  return c2b::sweep_rev_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, F, bZ, bt, bc, bU, bW, bY, flags, scratch, scratch_bytes,
+                                          stream, seg);
 }
 
 }  // extern "C"

@@ -13,8 +13,21 @@ struct ScanBuffers {
   int64_t node_stride = 0;
 };
 
+// One op of a series that is split into contiguous segments (one per GPU): see c2b_segment_t in the public header.
+//   phase 0: the whole op (default).  phase 1: summary pass + up-sweep, the segment's summary element goes to
+//   summary_out (the tree stays in the caller's scratch).  phase 2: state_in seeds the top of the tree, down-sweep,
+//   apply pass; reverse ops hand the bt term owed to the row just outside the segment to edge_out.
+struct Seg {
+  int phase;
+  const double *state_in;
+  double *summary_out;
+  double *edge_out;
+};
+
 struct SweepArgs {
   int64_t N, batch, C, L;
+  Seg seg;
+  int64_t tmin, tmax;  // valid time-stamp indices: [0, N-1], or [-1, ...] / [..., N] for a segment with a neighbour
   int J, K;
   const double *t, *c, *A, *B, *Y;  // A = "output" vector (dotted with the state), B = "input" vector
   double *Z, *F;
@@ -27,6 +40,8 @@ struct SweepArgs {
 
 struct SweepRevArgs {
   int64_t N, batch, C, L;
+  Seg seg;
+  int64_t tmin, tmax;
   int J, K;
   const double *t, *c, *A, *B, *Y, *Z, *F, *bZ;
   double *bt, *bA, *bB, *bY;
@@ -40,6 +55,8 @@ struct SweepRevArgs {
 
 struct FactorArgs {
   int64_t N, batch, C, L;
+  Seg seg;
+  int64_t tmin, tmax;
   int J;
   const double *t, *c, *a, *U, *V;
   double *d, *W, *S;
@@ -52,6 +69,8 @@ struct FactorArgs {
 
 struct FactorRevArgs {
   int64_t N, batch, C, L;
+  Seg seg;
+  int64_t tmin, tmax;
   int J;
   const double *t, *c, *U, *d, *W, *S, *bd, *bW;
   double *bt, *ba, *bU, *bV;
@@ -71,5 +90,11 @@ template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream);
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream);
+// state entering segment `which` of nseg from the segments' summaries; kind: 0 factor, 1 factor_rev (inst_factor.cu),
+// 2 solve_lower, 3 solve_lower_rev (inst_sweep.cu, K = 1)
+template <int JT>
+int launch_seg_carry_factor(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream);
+template <int JT>
+int launch_seg_carry_sweep(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream);
 
 }  // namespace c2b

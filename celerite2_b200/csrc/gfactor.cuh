@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
       double *tb       = gbuf + (k & 1) * TB;
       cp.run(tb, U + lo * J, rows * J, wide);
       cp.run(tb + oV, V + lo * J, rows * J, wide);
-      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.N);
+      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.tmin, g.tmax);
       cp.run(tb + oA, a + lo, rows, false);
     }
     cp_async_commit();
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
       for (int j = 0; j < J; ++j) tmp = fma(u[j], Sg[j], tmp);
       const double dn = a_n - gsum<G>(tmp * u_c);
       if (alive && c == G - 1) d[n] = dn;
-      if (alive && n >= 1 && dn <= 0.0) {
+      if (alive && n > g.tmin && dn <= 0.0) {
         if (c == 0) record_failure(g.status ? g.status + b : nullptr, n);
         alive = false;  // forward.hpp:128: later rows stay untouched (lanes keep participating in the barriers)
       }
@@ -204,7 +204,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_summary_kernel(Facto
       double *tb       = gbuf + (k & 1) * TB;
       cp.run(tb, U + lo * J, rows * J, wide);
       cp.run(tb + oV, V + lo * J, rows * J, wide);
-      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.N);
+      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.tmin, g.tmax);
       cp.run(tb + oA, a + lo, rows, false);
     }
     cp_async_commit();

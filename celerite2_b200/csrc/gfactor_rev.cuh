@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       cp.run(tb + oU + pad * J, U + lo * J, rows * J, wide);
       cp.run(tb + oW + pad * J, W + lo * J, rows * J, wide);
       cp.run(tb + oB + pad * J, bW + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, g.N);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, g.tmin, g.tmax);
       cp.run(tb + oD + pad, d + lo, rows, false);
       cp.run(tb + oE + pad, bd + lo, rows, false);
     }
@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       const int s     = R - 1 - r;
       const bool live = r < rows;
       const int64_t n = nt - r;
-      const bool nb   = live && n >= 1;
+      const bool nb   = live && n > g.tmin;
       double w[J], u[J], p[J], Sn[J];  // Sn[j] = S_n(j, c)
       lds_row<J>(tb + oU + s * J, u);
       lds_row<J>(tb + oW + s * J, w);

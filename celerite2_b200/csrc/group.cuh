@@ -183,12 +183,13 @@ struct GCopy {
       for (int e = c; e < cnt; e += G) cp_async8(dst + e, src + e);
     }
   }
-  // time stamps with one neighbour on either side: dst[e] = t[clamp(first + e, 0, N-1)], e < cnt.  The clamp makes
-  // dt = 0 (propagator exactly 1) at the two ends of the series, which is what the recursions want there.
-  C2B_DEV void run_t(double *dst, const double *t, int64_t first, int cnt, int64_t N) const {
+  // time stamps with one neighbour on either side: dst[e] = t[clamp(first + e, lo, hi)], e < cnt, [lo, hi] = [0, N-1]
+  // for a whole series.  The clamp makes dt = 0 (propagator exactly 1) at the two ends of the series, which is what
+  // the recursions want there; a segment of a longer series has a real neighbour at -1 and / or N instead.
+  C2B_DEV void run_t(double *dst, const double *t, int64_t first, int cnt, int64_t lo, int64_t hi) const {
     for (int e = c; e < cnt; e += G) {
       int64_t i = first + e;
-      i         = i < 0 ? 0 : (i > N - 1 ? N - 1 : i);
+      i         = i < lo ? lo : (i > hi ? hi : i);
       cp_async8(dst + e, t + i);
     }
   }

@@ -62,7 +62,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
       double *tb       = gbuf + (k & 1) * TB;
       cp.run(tb + pad * J, A + lo * J, rows * J, wide);
       cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
       cp.run(tb + oY + pad, Y + lo, rows, false);
       if (!SOLVE) cp.run(tb + oZ + pad, Z + lo, rows, false);
     }
@@ -157,7 +157,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
       double *tb       = gbuf + (k & 1) * TB;
       cp.run(tb + pad * J, A + lo * J, rows * J, wide);
       cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
       cp.run(tb + oY + pad, Y + lo, rows, false);
     }
     cp_async_commit();
@@ -265,7 +265,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
       cp.run(tb + pad * J, A + lo * J, rows * J, wide);
       cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
       cp.run(tb + oF + pad * J, F + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
       cp.run(tb + oZ + pad, bZ + lo, rows, false);
       cp.run(tb + oY + pad, ZY + lo, rows, false);
     }
@@ -274,7 +274,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
   issue(0);
   issue(1);
   const int64_t nf    = UP ? n0 : n1 - 1;  // first row visited
-  const int64_t nlast = LOWER ? 0 : a.N - 1;  // the row without a predecessor in this direction
+  const int64_t nlast = LOWER ? a.tmin : a.tmax;  // the row without a predecessor in this direction
   for (int k = 0; k < ttrips; ++k) {
     cp_async_wait<1>();
     __syncwarp();
@@ -385,7 +385,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(S
       double *tb       = gbuf + (k & 1) * TB;
       cp.run(tb + pad * J, A + lo * J, rows * J, wide);
       cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
       cp.run(tb + oZ + pad, bZ + lo, rows, false);
     }
     cp_async_commit();
@@ -393,7 +393,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(S
   issue(0);
   issue(1);
   const int64_t nf    = UP ? n0 : n1 - 1;
-  const int64_t nlast = LOWER ? 0 : a.N - 1;
+  const int64_t nlast = LOWER ? a.tmin : a.tmax;
   for (int k = 0; k < ttrips; ++k) {
     cp_async_wait<1>();
     __syncwarp();
@@ -457,10 +457,10 @@ struct CtaCopy {
       for (int e = c; e < cnt; e += n) cp_async8(dst + e, src + e);
     }
   }
-  C2B_DEV void run_t(double *dst, const double *t, int64_t first, int cnt, int64_t N) const {
+  C2B_DEV void run_t(double *dst, const double *t, int64_t first, int cnt, int64_t lo, int64_t hi) const {
     for (int e = c; e < cnt; e += n) {
       int64_t i = first + e;
-      i         = i < 0 ? 0 : (i > N - 1 ? N - 1 : i);
+      i         = i < lo ? lo : (i > hi ? hi : i);
       cp_async8(dst + e, t + i);
     }
   }
@@ -527,7 +527,7 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
         double *tb       = cs_smem + (kt & 1) * TB;
         cp.run(tb + pad * J, A + lo * J, rows * J, wide);
         cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-        cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.N);
+        cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
         for (int r = 0; r < rows; ++r) cp.run(tb + oY + (pad + r) * yw, Y + (lo + r) * (int64_t)a.K + kc0, kw, false);
       }
       cp_async_commit();

@@ -36,18 +36,30 @@ static int launch_factor_fast(FactorArgs &g, const ScanBuffers &sb, cudaStream_t
   return C2B_OK;
 }
 
-// compile-time widths up to 16: lane-group kernels (gfactor.cuh)
+// compile-time widths up to 16: lane-group kernels (gfactor.cuh).  seg.phase: see args.cuh.
 template <int JT>
 static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
   if constexpr (JT > 0 && JT <= 16) {
     constexpr int GP    = kGroupThreads / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((g.batch * g.C + GP - 1) / GP);
-    if (g.C > 1) {
+    const int phase     = g.seg.phase;
+    int rc;
+    if (g.C > 1 || phase != 0) {
       g.leaves      = sb.nodes;
       g.node_stride = sb.node_stride;
+    }
+    if ((phase == 0 && g.C > 1) || phase == 1)
       C2B_LAUNCH("gfactor_summary_kernel", stream, gfactor_summary_kernel<JT><<<grid, kGroupThreads, 0, stream>>>(g));
-      int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
-      if (rc) return rc;
+    if (phase == 1) {
+      if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
+      return seg_export_root<Lft<JT>>(g.J, 1, g.C, sb.nodes, g.seg.summary_out, stream);
+    }
+    if (phase == 2) {
+      if ((rc = seg_import_state<Lft<JT>>(g.J, 1, g.C, sb.states, g.seg.state_in, stream))) return rc;
+      if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      g.carry = sb.states;
+    } else if (g.C > 1) {
+      if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       g.carry = sb.states;
     }
     C2B_LAUNCH("gfactor_apply_kernel", stream, gfactor_apply_kernel<JT><<<grid, kGroupThreads, 0, stream>>>(g));
@@ -57,7 +69,11 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
 
 template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
-  if (JT > 0 && JT <= 16 && !getenv("C2B_NO_GROUP")) return launch_factor_group<JT>(g, sb, stream);
+  if (g.seg.phase != 0 && !(JT > 0 && JT <= 16)) {
+    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !getenv("C2B_NO_GROUP"))) return launch_factor_group<JT>(g, sb, stream);
   if (JT > 0 && getenv("C2B_TMA")) return launch_factor_fast<JT>(g, sb, stream);  // experimental, see DESIGN.md
   unsigned grid, block;
   size_t smem;
@@ -83,24 +99,42 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
   if constexpr (JT > 0 && JT <= 16) {
     constexpr int GP    = kGroupThreadsR / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((g.batch * g.C + GP - 1) / GP);
-    if (g.C > 1) {
+    const int phase     = g.seg.phase;
+    int rc;
+    if (g.C > 1 || phase != 0) {
       g.leaves      = sb.nodes;
       g.node_stride = sb.node_stride;
+    }
+    if ((phase == 0 && g.C > 1) || phase == 1)
       C2B_LAUNCH("gfactor_rev_summary_kernel", stream, gfactor_rev_kernel<JT, false><<<grid, kGroupThreadsR, 0, stream>>>(g));
-      int rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
-      if (rc) return rc;
+    if (phase == 1) {
+      if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
+      return seg_export_root<Cong<JT>>(g.J, 1, g.C, sb.nodes, g.seg.summary_out, stream);
+    }
+    if (phase == 2) {
+      if ((rc = seg_import_state<Cong<JT>>(g.J, 1, g.C, sb.states, g.seg.state_in, stream))) return rc;
+      if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      g.carry = sb.states;
+    } else if (g.C > 1) {
+      if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       g.carry = sb.states;
     }
     C2B_LAUNCH("gfactor_rev_apply_kernel", stream, gfactor_rev_kernel<JT, true><<<grid, kGroupThreadsR, 0, stream>>>(g));
     C2B_LAUNCH("rev_finalize_kernel", stream,
                rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
+    if (phase == 2 && g.seg.edge_out)
+      C2B_CUDA(cudaMemcpyAsync(g.seg.edge_out, g.bt_edge, sizeof(double), cudaMemcpyDeviceToDevice, stream));
   }
   return C2B_OK;
 }
 
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
-  if (JT > 0 && JT <= 16 && !getenv("C2B_NO_GROUP")) return launch_factor_rev_group<JT>(g, sb, bc, stream);
+  if (g.seg.phase != 0 && !(JT > 0 && JT <= 16)) {
+    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !getenv("C2B_NO_GROUP"))) return launch_factor_rev_group<JT>(g, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
@@ -121,6 +155,14 @@ int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaS
   return C2B_OK;
 }
 
+template <int JT>
+int launch_seg_carry_factor(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream) {
+  // factor walks upwards (earlier segments = lower rows), factor_rev downwards
+  if (kind == 0) return run_seg_carry<Lft<JT>>(JT, 1, nseg, which, false, summaries, out, stream);
+  return run_seg_carry<Cong<JT>>(JT, 1, nseg, which, true, summaries, out, stream);
+}
+
+template int launch_seg_carry_factor<C2B_JT>(int, int, int, const double *, double *, cudaStream_t);
 template int launch_factor<C2B_JT>(FactorArgs &, const ScanBuffers &, cudaStream_t);
 template int launch_factor_rev<C2B_JT>(FactorRevArgs &, const ScanBuffers &, double *, cudaStream_t);
 

@@ -11,18 +11,32 @@
 
 namespace c2b {
 
-// K == 1 solves with a compile-time width up to 8: lane-group kernels (gsweep.cuh)
+// K == 1 solves with a compile-time width up to 8: lane-group kernels (gsweep.cuh).  seg.phase selects the whole op
+// or one of the two halves of a segment of a longer series (args.cuh).
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   if constexpr (JT > 0 && JT <= 8 && SOLVE) {
-    if (a.C > 1) {
+    const int phase = a.seg.phase;
+    int rc;
+    if (a.C > 1 || phase != 0) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
+    }
+    if ((phase == 0 && a.C > 1) || phase == 1) {
       constexpr int GPS   = kGroupThreadsS / GroupOf<JT + 1>::G;
       const unsigned grid = (unsigned)((a.batch * a.C + GPS - 1) / GPS);
       C2B_LAUNCH("gsweep_summary_kernel", stream, gsweep_summary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
-      int rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
-      if (rc) return rc;
+    }
+    if (phase == 1) {
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
+      return seg_export_root<AffV<JT>>(a.J, 1, a.C, sb.nodes, a.seg.summary_out, stream);
+    }
+    if (phase == 2) {
+      if ((rc = seg_import_state<AffV<JT>>(a.J, 1, a.C, sb.states, a.seg.state_in, stream))) return rc;
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      a.carry = sb.states;
+    } else if (a.C > 1) {
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       a.carry = sb.states;
     }
     constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
@@ -35,14 +49,27 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   if constexpr (JT > 0 && JT <= 8 && SOLVE) {
-    if (a.C > 1) {
+    const int phase = a.seg.phase;
+    int rc;
+    if (a.C > 1 || phase != 0) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
+    }
+    if ((phase == 0 && a.C > 1) || phase == 1) {
       constexpr int GPS   = kGroupThreadsS / GroupOf<JT + 1>::G;
       const unsigned grid = (unsigned)((a.batch * a.C + GPS - 1) / GPS);
       C2B_LAUNCH("gsweep_rev_summary_kernel", stream, gsweep_rev_summary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
-      int rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
-      if (rc) return rc;
+    }
+    if (phase == 1) {
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
+      return seg_export_root<AffV<JT>>(a.J, 1, a.C, sb.nodes, a.seg.summary_out, stream);
+    }
+    if (phase == 2) {
+      if ((rc = seg_import_state<AffV<JT>>(a.J, 1, a.C, sb.states, a.seg.state_in, stream))) return rc;
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      a.carry = sb.states;
+    } else if (a.C > 1) {
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       a.carry = sb.states;
     }
     constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
@@ -50,6 +77,8 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     C2B_LAUNCH("gsweep_rev_apply_kernel", stream, gsweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
     C2B_LAUNCH("rev_finalize_kernel", stream,
                rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
+    if (phase == 2 && a.seg.edge_out)  // the chunk at the far end of the sweep owes its term to the neighbouring segment
+      C2B_CUDA(cudaMemcpyAsync(a.seg.edge_out, a.bt_edge + (LOWER ? 0 : a.C - 1), sizeof(double), cudaMemcpyDeviceToDevice, stream));
   }
   return C2B_OK;
 }
@@ -82,8 +111,13 @@ static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_
 
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if (a.seg.phase != 0 && !(JT > 0 && JT <= 8 && SOLVE && a.K == 1)) {
+    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 2, 4, 6 only");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+    return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
   if (JT > 0 && SOLVE && a.K > 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
-  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
@@ -117,7 +151,11 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
 
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
-  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && !getenv("C2B_NO_GROUP"))
+  if (a.seg.phase != 0 && !(JT > 0 && JT <= 8 && SOLVE && a.K == 1)) {
+    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 2, 4, 6 only");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
     return launch_sweep_rev_group<JT, SOLVE, LOWER>(a, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
@@ -152,6 +190,14 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
   C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   return C2B_OK;
 }
+
+template <int JT>
+int launch_seg_carry_sweep(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream) {
+  // solve_lower walks upwards, solve_lower_rev downwards
+  return run_seg_carry<AffV<JT>>(JT, 1, nseg, which, kind == 3, summaries, out, stream);
+}
+
+template int launch_seg_carry_sweep<C2B_JT>(int, int, int, const double *, double *, cudaStream_t);
 
 #define INST(S, L)                                                                                                                        \
   template int launch_sweep<C2B_JT, S, L>(SweepArgs &, const ScanBuffers &, cudaStream_t);                                                \

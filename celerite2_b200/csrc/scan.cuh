@@ -293,9 +293,11 @@ static inline void scan_sizes(int J, int K, int64_t batch, int64_t leaves, size_
 }
 
 // Leaves must already be in nodes[b][0..leaves).  On return states[b][i] (i < leaves) is the carry into chunk i.
+// mode 0: everything.  mode 1: up-sweep only (the root summary ends up in nodes[b][lv.off[top]]).  mode 2: down-sweep
+// only, from a root state the caller has put into states[b][lv.off[top]] (segments of a longer series).
 template <class Mon>
 static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *nodes, double *states, const double *init,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, int mode = 0) {
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop) {
@@ -352,16 +354,32 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
     int bases[kMaxLevels], nb = 0;
     for (int lb = 0; lb < top || nb == 0; lb += nlev) bases[nb++] = lb;
     auto grid_of = [&](int lb) { return dim3((unsigned)(batch * ((lv.count[lb] + (1 << nlev) - 1) >> nlev)), nslices); };
-    for (int q = 0; q + 1 < nb; ++q)
-      C2B_LAUNCH("scan_up_block", stream,
-                 (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
-    C2B_LAUNCH("scan_top_block", stream,
-               (scan_block<Mon, 2><<<grid_of(bases[nb - 1]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
-    for (int q = nb - 2; q >= 0; --q)
-      C2B_LAUNCH("scan_down_block", stream,
-                 (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+    if (mode == 0) {
+      for (int q = 0; q + 1 < nb; ++q)
+        C2B_LAUNCH("scan_up_block", stream,
+                   (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+      C2B_LAUNCH("scan_top_block", stream,
+                 (scan_block<Mon, 2><<<grid_of(bases[nb - 1]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
+      for (int q = nb - 2; q >= 0; --q)
+        C2B_LAUNCH("scan_down_block", stream,
+                   (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+    } else if (mode == 1) {
+      if (top > 0)
+        for (int q = 0; q < nb; ++q)
+          C2B_LAUNCH("scan_up_block", stream,
+                     (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+    } else {
+      if (top > 0)
+        for (int q = nb - 1; q >= 0; --q)
+          C2B_LAUNCH("scan_down_block", stream,
+                     (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+    }
     return C2B_OK;
   } else {
+  if (mode != 0) {
+    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
   const int threads  = 128;  // 4 warps
   const int64_t warps = batch * nblk;
   const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
@@ -373,6 +391,63 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   }
   C2B_LAUNCH("scan_down_warp", stream, scan_down_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes, states, init));
   return C2B_OK;
+  }
+}
+
+// Segment plumbing shared by the launchers (batch == 1): where the root of the tree lives
+template <class Mon>
+static inline int seg_export_root(int J, int K, int64_t leaves, const double *nodes, double *summary_out, cudaStream_t stream) {
+  const Levels lv = make_levels(leaves);
+  const int es    = Mon::esize(J, K);
+  C2B_CUDA(cudaMemcpyAsync(summary_out, nodes + lv.off[lv.nlev - 1] * es, sizeof(double) * es, cudaMemcpyDeviceToDevice, stream));
+  return C2B_OK;
+}
+template <class Mon>
+static inline int seg_import_state(int J, int K, int64_t leaves, double *states, const double *state_in, cudaStream_t stream) {
+  const Levels lv = make_levels(leaves);
+  const int ss    = Mon::ssize(J, K);
+  double *dst     = states + lv.off[lv.nlev - 1] * ss;
+  if (state_in)
+    C2B_CUDA(cudaMemcpyAsync(dst, state_in, sizeof(double) * ss, cudaMemcpyDeviceToDevice, stream));
+  else
+    C2B_CUDA(cudaMemsetAsync(dst, 0, sizeof(double) * ss, stream));
+  return C2B_OK;
+}
+
+// State entering segment `which`: the summaries of the segments that come earlier in processing order, applied one
+// after the other to the zero state by one warp (at most a handful of segments: one per GPU).
+template <class Mon>
+__global__ void __launch_bounds__(32) seg_carry_kernel(int J_, int K, int nseg, int which, bool descending, const double *summaries,
+                                                       double *out) {
+  const int J = Mon::kJT ? Mon::kJT : J_;
+  extern __shared__ __align__(16) double sc_sm[];
+  const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
+  double *e = sc_sm, *s0 = e + es, *s1 = s0 + ss, *scratch = s1 + ss;
+  const int lane = threadIdx.x;
+  for (int i = lane; i < ss; i += 32) s0[i] = 0.0;
+  __syncwarp();
+  const int step = descending ? -1 : 1;
+  for (int s = descending ? nseg - 1 : 0; s != which; s += step) {
+    wcopy(lane, es, summaries + (size_t)s * es, e);
+    __syncwarp();
+    Coop<Mon>::wapply(lane, J, K, e, s0, s1, scratch);
+    double *tmp = s0;
+    s0          = s1;
+    s1          = tmp;
+  }
+  wcopy(lane, ss, s0, out);
+}
+template <class Mon>
+static inline int run_seg_carry(int J, int K, int nseg, int which, bool descending, const double *summaries, double *out,
+                                cudaStream_t stream) {
+  if constexpr (Mon::kCoop) {
+    const size_t smem = (size_t)(Mon::esize(J, K) + 2 * Mon::ssize(J, K) + Coop<Mon>::wsmem(J, K)) * sizeof(double);
+    if (smem > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(seg_carry_kernel<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    C2B_LAUNCH("seg_carry_kernel", stream, (seg_carry_kernel<Mon><<<1, 32, smem, stream>>>(J, K, nseg, which, descending, summaries, out)));
+    return C2B_OK;
+  } else {
+    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    return C2B_ERR_INVALID_ARGUMENT;
   }
 }
 

@@ -105,6 +105,55 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
                                   int32_t flags, void *scratch, size_t scratch_bytes, void *stream);
 
 /*
+ * ---- One series split into contiguous segments (one per GPU) ------------------------------------------------------------
+ * No reference counterpart: the reference is sequential over N ("one long series").  A segment is a
+ * run of rows [r0, r1) of the series; the caller passes pointers to the segment's first row (t + r0, U + r0*J, ...) and
+ * N = r1 - r0.  The time stamps of the neighbouring rows must be addressable through the same pointer when has_left /
+ * has_right say so (t[-1], t[N]): replicate t on every device or keep a one-element halo.  batch must be 1 and the
+ * width one of the compiled ones (J in 2, 4, 6, 16; sweeps: J <= 6, K = 1).  Each of the four operators of the
+ * log-likelihood + gradient pipeline runs in two calls with the SAME scratch buffer (which holds the tree in between):
+ *   phase C2B_SEG_SUMMARISE: summary pass + up-sweep; the segment's summary element (c2b_segment_sizes doubles) is
+ *                            written to summary_out.  Exchange the summaries of all segments (all-gather),
+ *   c2b_segment_carry:       folds the summaries of the segments that come earlier in the operator's processing order
+ *                            (lower rows for factor / solve_lower, higher rows for the two reverse operators) into
+ *                            the state entering this segment,
+ *   phase C2B_SEG_APPLY:     state_in -> down-sweep -> apply pass; outputs as for the plain entry point, for this
+ *                            segment's rows.  Reverse operators also return in edge_out the one bt term owed to the row
+ *                            just below the segment (add it to the last bt of the lower neighbour); bc is this
+ *                            segment's partial sum (add over segments).
+ */
+typedef struct c2b_segment {
+  int32_t phase;     /* C2B_SEG_SUMMARISE or C2B_SEG_APPLY */
+  int32_t has_left;  /* the series continues below row 0 of the segment */
+  int32_t has_right; /* the series continues above row N-1 */
+  int32_t reserved;
+  const double *state_in; /* APPLY: device, c2b_segment_sizes state doubles; NULL = zero state */
+  double *summary_out;    /* SUMMARISE: device, c2b_segment_sizes summary doubles */
+  double *edge_out;       /* APPLY, reverse operators: device, 1 double; may be NULL */
+} c2b_segment_t;
+#define C2B_SEG_SUMMARISE 1
+#define C2B_SEG_APPLY 2
+
+int c2b_segment_sizes(int32_t op, int32_t J, int32_t K, int64_t *summary_doubles, int64_t *state_doubles);
+/* summaries: device, nseg elements in series order.  state_out: device.  op as for c2b_scratch_bytes. */
+int c2b_segment_carry(int32_t op, int32_t J, int32_t K, int32_t nseg, int32_t which, const double *summaries, double *state_out,
+                      void *stream);
+int c2b_factor_segment(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U,
+                       const double *V, double *d, double *W, double *S, int64_t *status, int32_t flags, void *scratch,
+                       size_t scratch_bytes, void *stream, const c2b_segment_t *seg);
+int c2b_factor_rev_segment(int64_t N, int32_t J, int64_t batch, const double *t, const double *c, const double *a, const double *U,
+                           const double *V, const double *d, const double *W, const double *S, const double *bd, const double *bW,
+                           double *bt, double *bc, double *ba, double *bU, double *bV, int32_t flags, void *scratch,
+                           size_t scratch_bytes, void *stream, const c2b_segment_t *seg);
+int c2b_solve_lower_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                            const double *W, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                            void *stream, const c2b_segment_t *seg);
+int c2b_solve_lower_rev_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                                const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                                double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                                void *stream, const c2b_segment_t *seg);
+
+/*
  * LDL^T factorisation.  Replaces celerite2::core::factor, c++/include/celerite2/forward.hpp:69-135
  * (S != NULL) and the no-workspace overload c++/include/celerite2/interface.hpp:37-48 (S == NULL).
  * d may alias a and W may alias V (forward.hpp:55-58).
