@@ -35,7 +35,7 @@ _EXTRA = {
     "api_misc.cu": ["misc.cuh"],
     "api_pipeline.cu": ["misc.cuh"],
     "inst_sweep.cu": ["sweep.cuh", "group.cuh", "gsweep.cuh"],
-    "inst_factor.cu": ["factor.cuh", "fast_factor.cuh", "tile.cuh", "group.cuh", "gfactor.cuh", "gfactor_rev.cuh"],
+    "inst_factor.cu": ["factor.cuh", "group.cuh", "gfactor.cuh", "gfactor_rev.cuh"],
 }
 
 

@@ -3,7 +3,6 @@
 
 #include "host_common.cuh"
 #include "factor.cuh"
-#include "fast_factor.cuh"
 #include "gfactor.cuh"
 #include "gfactor_rev.cuh"
 
@@ -12,29 +11,6 @@
 #endif
 
 namespace c2b {
-
-// compile-time widths: TMA tile pipeline (fast_factor.cuh)
-template <int JT>
-static int launch_factor_fast(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
-  if constexpr (JT > 0 && JT <= 8) {
-    using Lay = FFactorLayout<JT>;
-    const unsigned grid = (unsigned)((g.batch * g.C + 31) / 32);
-    if (g.C > 1) {
-      g.leaves      = sb.nodes;
-      g.node_stride = sb.node_stride;
-      const size_t sm1 = TilePipe<kFT, Lay::SIN, Lay::SOUT_SUMMARY>::kSmemBytes;
-      if (sm1 > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(ffactor_summary_kernel<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
-      C2B_LAUNCH("ffactor_summary_kernel", stream, ffactor_summary_kernel<JT><<<grid, 32, sm1, stream>>>(g));
-      int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
-      if (rc) return rc;
-      g.carry = sb.states;
-    }
-    const size_t sm2 = TilePipe<kFT, Lay::SIN, Lay::SOUT>::kSmemBytes;
-    if (sm2 > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(ffactor_apply_kernel<JT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
-    C2B_LAUNCH("ffactor_apply_kernel", stream, ffactor_apply_kernel<JT><<<grid, 32, sm2, stream>>>(g));
-  }
-  return C2B_OK;
-}
 
 // compile-time widths up to 16: lane-group kernels (gfactor.cuh).  seg.phase: see args.cuh.
 template <int JT>
@@ -74,7 +50,6 @@ int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
     return C2B_ERR_INVALID_ARGUMENT;
   }
   if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !getenv("C2B_NO_GROUP"))) return launch_factor_group<JT>(g, sb, stream);
-  if (JT > 0 && getenv("C2B_TMA")) return launch_factor_fast<JT>(g, sb, stream);  // experimental, see DESIGN.md
   unsigned grid, block;
   size_t smem;
   int rcs;
