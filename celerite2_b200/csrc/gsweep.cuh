@@ -210,6 +210,169 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
   }
 }
 
+// ---- forward summary, matmuls: diagonal-affine chunk map G -> m o G + b, lane c holding element c ----------------------
+// tile buffer: B[R*J] | t[R+2] y[R]
+template <int J, bool LOWER>
+__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_msummary_kernel(SweepArgs a) {
+  constexpr int G  = GroupOf<J>::G;
+  constexpr int GP = kGroupThreadsS / G;
+  constexpr int R  = kTileRows;
+  constexpr int JE = (J + 1) & ~1;
+  constexpr int oT = R * J, oY = oT + R + 2;
+  constexpr int TB = (oY + R + 1) & ~1;
+  constexpr int GS = GTileStride<G, TB, 2>::value;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ double scc[GP * JE];
+  const int c         = threadIdx.x & (G - 1);
+  const int gin       = threadIdx.x / G;
+  const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
+  const bool has      = unit < a.batch * a.C;
+  const bool act      = has && c < J;
+  const int cj        = c < J ? c : 0;
+  const int64_t chunk = has ? unit % a.C : 0, b = has ? unit / a.C : 0;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
+  const double *t     = a.t + b * a.t_bs;
+  const double *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
+  double *gbuf = stile + gin * GS;
+  const GCopy<G> cp{c};
+  const bool wide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(B) & 15) == 0);
+  const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
+  double Fc = 0.0, mc = 1.0;
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = LOWER ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
+      const int pad    = LOWER ? 0 : R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb + pad * J, B + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
+      cp.run(tb + oY + pad, Y + lo, rows, false);
+    }
+    cp_async_commit();
+  };
+  issue(0);
+  issue(1);
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    double p[R];
+    eval_props_reg<J, G, R>(pairs, c, cc, [&](int r) {
+      const int s = LOWER ? r : R - 1 - r;
+      return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+    }, p);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s = LOWER ? r : R - 1 - r;
+      if (r < rows) {
+        mc *= p[r];
+        Fc = fma(act ? tb[s * J + cj] : 0.0, tb[oY + s], p[r] * Fc);
+      }
+    }
+    __syncwarp();
+    issue(k + 2);
+  }
+  if (act) {
+    const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
+    double *e          = a.leaves + (b * a.node_stride + leaf) * (int64_t)(2 * J);
+    e[c]               = mc;
+    e[J + c]           = Fc;
+  }
+}
+
+// ---- reverse summary, matmuls ------------------------------------------------------------------------------------------
+// tile buffer: A[R*J] | t[R+2] bZ[R]
+template <int J, bool LOWER>
+__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_msummary_kernel(SweepRevArgs a) {
+  constexpr int G   = GroupOf<J>::G;
+  constexpr int GP  = kGroupThreadsS / G;
+  constexpr int R   = kTileRows;
+  constexpr int JE  = (J + 1) & ~1;
+  constexpr int oT  = R * J, oZ = oT + R + 2;
+  constexpr int TB  = (oZ + R + 1) & ~1;
+  constexpr int GS  = GTileStride<G, TB, 2>::value;
+  constexpr bool UP = !LOWER;
+  constexpr int dir = UP ? 1 : -1;
+  __shared__ __align__(16) double stile[GP * GS];
+  __shared__ double scc[GP * JE];
+  const int c         = threadIdx.x & (G - 1);
+  const int gin       = threadIdx.x / G;
+  const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
+  const bool has      = unit < a.batch * a.C;
+  const bool act      = has && c < J;
+  const int cj        = c < J ? c : 0;
+  const int64_t chunk = has ? unit % a.C : 0, b = has ? unit / a.C : 0;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
+  const double *t     = a.t + b * a.t_bs;
+  const double *A = a.A + b * a.N * J, *bZ = a.bZ + b * a.N;
+  double *gbuf = stile + gin * GS;
+  const GCopy<G> cp{c};
+  const bool wide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0);
+  const double cc = act ? (a.c + b * a.c_bs)[c] : 0.0;
+  PropPairs<J> pairs;
+  if (c < J) scc[gin * JE + c] = cc;
+  __syncwarp();
+  pairs.init(scc + gin * JE, c);
+  double bF = 0.0, mc = 1.0;
+  const int cnt    = (int)(n1 - n0);
+  const int ntile  = (cnt + R - 1) / R;
+  const int ttrips = warp_max(ntile);
+  auto issue = [&](int k) {
+    if (k < ntile) {
+      const int rows   = cnt - k * R < R ? cnt - k * R : R;
+      const int64_t lo = UP ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
+      const int pad    = UP ? 0 : R - rows;
+      double *tb       = gbuf + (k & 1) * TB;
+      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
+      cp.run(tb + oZ + pad, bZ + lo, rows, false);
+    }
+    cp_async_commit();
+  };
+  issue(0);
+  issue(1);
+  const int64_t nf    = UP ? n0 : n1 - 1;
+  const int64_t nlast = LOWER ? a.tmin : a.tmax;
+  for (int k = 0; k < ttrips; ++k) {
+    cp_async_wait<1>();
+    __syncwarp();
+    const double *tb = gbuf + (k & 1) * TB;
+    const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
+    double p[R];
+    eval_props_reg<J, G, R>(pairs, c, cc, [&](int r) {
+      const int s = UP ? r : R - 1 - r;
+      return LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+    }, p);
+    const int64_t nt = nf + (int64_t)dir * k * R;
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int s = UP ? r : R - 1 - r;
+      if (r < rows && nt + dir * r != nlast) {
+        mc *= p[r];
+        bF = p[r] * fma(act ? tb[s * J + cj] : 0.0, tb[oZ + s], bF);  // bF <- p (bF + a bZ)
+      }
+    }
+    __syncwarp();
+    issue(k + 2);
+  }
+  if (act) {
+    const int64_t leaf = LOWER ? a.C - 1 - chunk : chunk;
+    double *e          = a.leaves + (b * a.node_stride + leaf) * (int64_t)(2 * J);
+    e[c]               = mc;
+    e[J + c]           = bF;
+  }
+}
+
 // ---- reverse apply -----------------------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] F[R*J] | t[R+2] bZ[R] (Z or Y)[R]
 template <int J, bool SOLVE, bool LOWER>

@@ -15,6 +15,20 @@ namespace c2b {
 // or one of the two halves of a segment of a longer series (args.cuh).
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 8 && !SOLVE) {
+    // matmuls: diagonal-affine chunk maps
+    constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
+    const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
+    if (a.C > 1) {
+      a.leaves      = sb.nodes;
+      a.node_stride = sb.node_stride;
+      C2B_LAUNCH("gsweep_msummary_kernel", stream, gsweep_msummary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      int rc = run_scan<DiagV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      a.carry = sb.states;
+    }
+    C2B_LAUNCH("gsweep_apply_kernel", stream, gsweep_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+  }
   if constexpr (JT > 0 && JT <= 8 && SOLVE) {
     const int phase = a.seg.phase;
     int rc;
@@ -48,6 +62,21 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
 
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 8 && !SOLVE) {
+    constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
+    const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
+    if (a.C > 1) {
+      a.leaves      = sb.nodes;
+      a.node_stride = sb.node_stride;
+      C2B_LAUNCH("gsweep_rev_msummary_kernel", stream, gsweep_rev_msummary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      int rc = run_scan<DiagV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      a.carry = sb.states;
+    }
+    C2B_LAUNCH("gsweep_rev_apply_kernel", stream, gsweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+    C2B_LAUNCH("rev_finalize_kernel", stream,
+               rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
+  }
   if constexpr (JT > 0 && JT <= 8 && SOLVE) {
     const int phase = a.seg.phase;
     int rc;
@@ -115,7 +144,7 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
     set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 2, 4, 6 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+  if (JT > 0 && JT <= 8 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
     return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
   if (JT > 0 && SOLVE && a.K > 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
@@ -155,7 +184,7 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
     set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 2, 4, 6 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 8 && SOLVE && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+  if (JT > 0 && JT <= 8 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
     return launch_sweep_rev_group<JT, SOLVE, LOWER>(a, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
