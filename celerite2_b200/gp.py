@@ -99,3 +99,60 @@ class HostLogLikelihood:
         self.out_h.copy_(self.out_d, non_blocking=True)
         main.synchronize()  # the caller needs the values
         return self.out_h, r["status"]
+
+
+class HostLogLikelihoodStream:
+    """Streaming form of HostLogLikelihood for callers that evaluate many series (or many parameter sets) in a row:
+    `submit` enqueues the uploads of one evaluation on a copy stream and its kernels on the caller's stream and returns
+    at once; `collect` waits for that evaluation's result.  With two slots the uploads of evaluation i+1 overlap the
+    kernels of evaluation i.  Results come back in submission order.
+    """
+
+    def __init__(self, N, coeff_shapes, device, slots=2):
+        self.dev = device
+        f8 = dict(dtype=torch.float64, device=device)
+        self.n_out = 1 + sum(int(torch.Size(sh).numel()) for sh in coeff_shapes)
+        self.copy = torch.cuda.Stream(device=device)
+        self.slots = []
+        for _ in range(slots):
+            self.slots.append(dict(
+                t=torch.empty(N, **f8), y=torch.empty(N, **f8), diag=torch.empty(N, **f8),
+                co=[torch.empty(tuple(sh), **f8) for sh in coeff_shapes],
+                out_d=torch.empty(self.n_out, **f8), out_h=torch.empty(self.n_out, dtype=torch.float64).pin_memory(),
+                td_ready=torch.cuda.Event(), y_ready=torch.cuda.Event(), done=torch.cuda.Event(), busy=False, status=None))
+        self.next, self.pending = 0, []
+
+    def submit(self, coeffs_h, t_h, y_h, diag_h):
+        sl = self.slots[self.next]
+        if sl["busy"]:
+            raise RuntimeError("all slots in flight: collect() a result first")
+        main = torch.cuda.current_stream()
+        # the slot's previous evaluation (kernels on `main`) has been collected, hence finished: its buffers are free
+        with torch.cuda.stream(self.copy):
+            for s, h in zip(sl["co"], coeffs_h):
+                s.copy_(h, non_blocking=True)
+            sl["t"].copy_(t_h, non_blocking=True)
+            sl["diag"].copy_(diag_h, non_blocking=True)
+            sl["td_ready"].record(self.copy)
+            sl["y"].copy_(y_h, non_blocking=True)
+            sl["y_ready"].record(self.copy)
+        main.wait_event(sl["td_ready"])
+        r = log_likelihood_and_grad(sl["co"], sl["t"], sl["y"], sl["diag"], y_ready=sl["y_ready"])
+        sl["out_d"][0:1].copy_(r["loglike"].reshape(1))
+        o = 1
+        for nm in COEFF_NAMES:
+            g = r["grads"][nm]
+            sl["out_d"][o:o + g.numel()].copy_(g.reshape(-1))
+            o += g.numel()
+        sl["out_h"].copy_(sl["out_d"], non_blocking=True)
+        sl["done"].record(main)
+        sl["busy"], sl["status"] = True, r["status"]
+        self.pending.append(self.next)
+        self.next = (self.next + 1) % len(self.slots)
+
+    def collect(self):
+        """-> (pinned host result of the oldest evaluation in flight, its status tensor); valid until the slot is reused"""
+        sl = self.slots[self.pending.pop(0)]
+        sl["done"].synchronize()
+        sl["busy"] = False
+        return sl["out_h"], sl["status"]

@@ -116,3 +116,35 @@ def test_host_buffer_entry_point_matches_device_pipeline():
         assert got.shape == want.shape
         assert np.max(np.abs(got - want) / np.maximum(1.0, np.abs(want))) < 1e-12
         assert abs(got[0] - _oracle_loglike(co, t, y, diag)) < 1e-10 * abs(got[0])
+
+
+def test_streaming_host_entry_point():
+    """HostLogLikelihoodStream: results in submission order, equal to the synchronous entry point, slots reused."""
+    import torch
+
+    from celerite2_b200 import gp
+    from celerite2_b200 import workloads as wl
+
+    dev = torch.device("cuda:0")
+    co = [np.array(v, dtype=np.float64) for v in ALL_KERNELS["c2_J6"]]
+    N = 40000
+    co_h = [torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for v in co]
+    sync = gp.HostLogLikelihood(N, [v.shape for v in co_h], dev)
+    stream = gp.HostLogLikelihoodStream(N, [v.shape for v in co_h], dev)
+    data = [[torch.from_numpy(v).pin_memory() for v in wl.light_curve(N, seed)] for seed in (4, 5, 6, 7, 8)]
+    want = [sync(co_h, *hs)[0].numpy().copy() for hs in data]
+    got = []
+    stream.submit(co_h, *data[0])
+    for hs in data[1:]:
+        stream.submit(co_h, *hs)
+        got.append(stream.collect()[0].numpy().copy())
+    got.append(stream.collect()[0].numpy().copy())
+    with pytest.raises(IndexError):
+        stream.collect()
+    for g, w in zip(got, want):
+        assert np.max(np.abs(g - w) / np.maximum(1.0, np.abs(w))) < 1e-12
+    stream.submit(co_h, *data[0])
+    stream.submit(co_h, *data[1])
+    with pytest.raises(RuntimeError):
+        stream.submit(co_h, *data[2])
+    stream.collect(), stream.collect()
