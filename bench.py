@@ -318,7 +318,8 @@ def run_ours(args):
             traffic = json.load(f).get(dom)  # DRAM bytes per call from the committed ncu --set full captures
     roofline = {
         "bound": "hbm", "kernel": dom + " (all kernels of the C-ABI call: summary + scan + apply)",
-        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "frac_of_nominal_8000_gbs": achieved / 8000.0,
+        "traffic": traffic,
         "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes, "ms_per_launch": per_op[dom],
         "whole_step": {"algorithmic_bytes": step_bytes, "achieved_gbs": step_bytes / (ms_step * 1e-3) / 1e9,
                        "frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
