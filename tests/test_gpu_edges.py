@@ -187,3 +187,46 @@ def test_factor_rev_accumulate_flag(env, name, chunks):
     assert relerr(H(ba), want[2]) < TOL
     assert relerr(H(bU), want[3] + pre[2]) < TOL
     assert relerr(H(bV), want[4]) < TOL
+
+
+@pytest.mark.parametrize("chunks", [0, 5])
+def test_pointers_aligned_to_8_bytes_only(env, chunks):
+    """The tile kernels copy with 16-byte cp.async when the arrays allow it; arrays that start on an odd multiple of
+    8 bytes must take the 8-byte path and give the same results."""
+    ops, T, H, torch = env
+    import oracle
+    from celerite2_b200 import workloads as wl
+
+    def off(x):  # same values, storage shifted by one double
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        buf = torch.empty(x.size + 1, dtype=torch.float64, device="cuda:0")
+        v = buf[1:].view(x.shape)
+        v.copy_(torch.from_numpy(x))
+        assert v.data_ptr() % 16 == 8
+        return v
+
+    P = oracle.port()
+    N = 1200
+    t, y, diag = wl.light_curve(N, 9)
+    c, a, U, V = P.get_celerite_matrices(*ALL_KERNELS["c2_J6"], t, diag)
+    _, d_r, W_r, S_r = P.factor(t, c, a, U, V)
+    Y = y[:, None]
+    Z_r, F_r = P.sweep("solve_lower", t, c, U, W_r, Y)
+    bz = np.cos(Z_r)
+    ops.set_chunks_per_series(chunks)
+    try:
+        d, W, S, st = ops.factor(off(t), off(c), off(a), off(U), off(V), d=off(a), W=off(V))
+        Z, F = ops.solve_lower(off(t), off(c), off(U), off(W_r), off(Y), workspace=True)
+        M, _ = ops.matmul_lower(off(t), off(c), off(U), off(V), off(Y))
+        got = ops.solve_lower_rev(off(t), off(c), off(U), off(W_r), off(Y), off(Z_r), off(F_r), off(bz))
+        got2 = ops.factor_rev(off(t), off(c), off(a), off(U), off(V), off(d_r), off(W_r), off(S_r.reshape(N, 6, 6)), off(np.sin(t)), off(np.cos(W_r)))
+    finally:
+        ops.set_chunks_per_series(0)
+    assert int(st.item()) == 0
+    assert relerr(H(d), d_r) < TOL and relerr(H(W), W_r) < TOL and relerr(H(S).reshape(N, -1), S_r) < TOL
+    assert relerr(H(Z), Z_r) < TOL and relerr(H(F), F_r) < TOL
+    assert relerr(H(M), P.sweep("matmul_lower", t, c, U, V, Y, workspace=False)[0]) < TOL
+    for u, v in zip(got, P.sweep_rev("solve_lower", t, c, U, W_r, Y, Z_r, F_r, bz)):
+        assert relerr(H(u), v) < TOL
+    for u, v in zip(got2, P.factor_rev(t, c, a, U, V, d_r, W_r, S_r, np.sin(t), np.cos(W_r))):
+        assert relerr(H(u), v) < TOL
