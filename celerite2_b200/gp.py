@@ -32,14 +32,15 @@ def log_likelihood(coeffs, t, y, diag, layout="blocked"):
     return ll, status
 
 
-def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grads=False, y_ready=None):
-    """-> dict(loglike, status, grads = {ar, cr, ac, bc, cc, dc} [, t, y, diag]).
-    y_ready: optional CUDA event after which y is valid (y is first read by solve_lower, so its upload can overlap the
-    assembly and the factorisation; see HostLogLikelihood)."""
+def _front(coeffs, t, diag, layout):
+    """the part of the pipeline that does not read y: assembly + factorisation"""
     c, a, U, V = ops.get_celerite_matrices(*coeffs, t, diag, layout=layout)
     d, W, S, status = ops.factor(t, c, a, U, V)
-    if y_ready is not None:
-        torch.cuda.current_stream().wait_event(y_ready)
+    return c, a, U, V, d, W, S, status
+
+
+def _back(coeffs, t, y, diag, front, layout, want_data_grads):
+    c, a, U, V, d, W, S, status = front
     Y = y.unsqueeze(-1)
     Z, F = ops.solve_lower(t, c, U, W, Y, workspace=True)
     out, bz, bd = ops.norm_logdet(d, Z.squeeze(-1), want_grad=True)
@@ -52,6 +53,53 @@ def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grad
     if want_data_grads:
         res["grads"].update(t=g[6], y=bY.squeeze(-1), diag=g[7])
     return res
+
+
+def log_likelihood_and_grad(coeffs, t, y, diag, layout="blocked", want_data_grads=False, y_ready=None):
+    """-> dict(loglike, status, grads = {ar, cr, ac, bc, cc, dc} [, t, y, diag]).
+    y_ready: optional CUDA event after which y is valid (y is first read by solve_lower, so its upload can overlap the
+    assembly and the factorisation; see HostLogLikelihood)."""
+    front = _front(coeffs, t, diag, layout)
+    if y_ready is not None:
+        torch.cuda.current_stream().wait_event(y_ready)
+    return _back(coeffs, t, y, diag, front, layout, want_data_grads)
+
+
+class GraphedLogLikelihood:
+    """log_likelihood_and_grad for FIXED input buffers, captured once in two CUDA graphs (the part that does not read y,
+    and the rest) and replayed: the ~40 kernel launches of an evaluation become two graph launches, which takes the
+    launch gaps out of the step.  Write new data into the tensors given here (or pass them to __call__), then replay.
+    The results live in fixed tensors that every replay overwrites.
+    """
+
+    def __init__(self, coeffs, t, y, diag, layout="blocked", warmup=2):
+        self.coeffs, self.t, self.y, self.diag = list(coeffs), t, y, diag
+        side = torch.cuda.Stream(device=t.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):  # warm-up off the capturing stream: scratch buffers, function attributes
+            for _ in range(warmup):
+                log_likelihood_and_grad(self.coeffs, t, y, diag, layout=layout)
+        torch.cuda.current_stream().wait_stream(side)
+        self.g_front, self.g_back = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.g_front):
+            self._front = _front(self.coeffs, t, diag, layout)
+        with torch.cuda.graph(self.g_back, pool=self.g_front.pool()):
+            self.result = _back(self.coeffs, t, y, diag, self._front, layout, False)
+
+    def replay_front(self):
+        self.g_front.replay()
+
+    def replay_back(self):
+        self.g_back.replay()
+        return self.result
+
+    def __call__(self, coeffs=None, t=None, y=None, diag=None):
+        for dst, src in list(zip(self.coeffs, coeffs or [])) + [(self.t, t), (self.y, y), (self.diag, diag)]:
+            if src is not None and src is not dst:
+                dst.copy_(src, non_blocking=True)
+        self.g_front.replay()
+        self.g_back.replay()
+        return self.result
 
 
 class HostLogLikelihood:
@@ -76,6 +124,7 @@ class HostLogLikelihood:
         self.y_ready = torch.cuda.Event()
         self.h2d_bytes = 8 * (3 * N + sum(v.numel() for v in self.co))
         self.d2h_bytes = 8 * self.n_out
+        self.graph = None  # captured at the first call (the staging buffers then hold real data)
 
     def __call__(self, coeffs_h, t_h, y_h, diag_h):
         main = torch.cuda.current_stream()
@@ -89,7 +138,12 @@ class HostLogLikelihood:
         with torch.cuda.stream(self.side):
             self.y.copy_(y_h, non_blocking=True)
             self.y_ready.record(self.side)
-        r = log_likelihood_and_grad(self.co, self.t, self.y, self.diag, y_ready=self.y_ready)
+        if self.graph is None:
+            main.wait_event(self.y_ready)
+            self.graph = GraphedLogLikelihood(self.co, self.t, self.y, self.diag)
+        self.graph.replay_front()
+        main.wait_event(self.y_ready)
+        r = self.graph.replay_back()
         self.out_d[0:1].copy_(r["loglike"].reshape(1))
         o = 1
         for nm in COEFF_NAMES:
@@ -119,7 +173,8 @@ class HostLogLikelihoodStream:
                 t=torch.empty(N, **f8), y=torch.empty(N, **f8), diag=torch.empty(N, **f8),
                 co=[torch.empty(tuple(sh), **f8) for sh in coeff_shapes],
                 out_d=torch.empty(self.n_out, **f8), out_h=torch.empty(self.n_out, dtype=torch.float64).pin_memory(),
-                td_ready=torch.cuda.Event(), y_ready=torch.cuda.Event(), done=torch.cuda.Event(), busy=False, status=None))
+                td_ready=torch.cuda.Event(), y_ready=torch.cuda.Event(), done=torch.cuda.Event(), busy=False, status=None,
+                graph=None))
         self.next, self.pending = 0, []
 
     def submit(self, coeffs_h, t_h, y_h, diag_h):
@@ -137,7 +192,12 @@ class HostLogLikelihoodStream:
             sl["y"].copy_(y_h, non_blocking=True)
             sl["y_ready"].record(self.copy)
         main.wait_event(sl["td_ready"])
-        r = log_likelihood_and_grad(sl["co"], sl["t"], sl["y"], sl["diag"], y_ready=sl["y_ready"])
+        if sl["graph"] is None:
+            main.wait_event(sl["y_ready"])
+            sl["graph"] = GraphedLogLikelihood(sl["co"], sl["t"], sl["y"], sl["diag"])
+        sl["graph"].replay_front()
+        main.wait_event(sl["y_ready"])
+        r = sl["graph"].replay_back()
         sl["out_d"][0:1].copy_(r["loglike"].reshape(1))
         o = 1
         for nm in COEFF_NAMES:

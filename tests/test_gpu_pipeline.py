@@ -148,3 +148,27 @@ def test_streaming_host_entry_point():
     with pytest.raises(RuntimeError):
         stream.submit(co_h, *data[2])
     stream.collect(), stream.collect()
+
+
+def test_graphed_pipeline_matches_eager():
+    """GraphedLogLikelihood: replays equal the eager pipeline, also after the input buffers were overwritten."""
+    import torch
+
+    from celerite2_b200 import gp
+    from celerite2_b200 import workloads as wl
+
+    dev = torch.device("cuda:0")
+    T = lambda x: torch.as_tensor(np.ascontiguousarray(x, dtype=np.float64), device=dev)
+    co = [T(np.array(v, dtype=np.float64)) for v in ALL_KERNELS["c2_J6"]]
+    N = 30000
+    t, y, diag = [T(v) for v in wl.light_curve(N, 12)]
+    g = gp.GraphedLogLikelihood(co, t, y, diag)
+    for seed in (12, 13):
+        tn, yn, dn = [T(v) for v in wl.light_curve(N, seed)]
+        r = g(t=tn, y=yn, diag=dn)
+        want = gp.log_likelihood_and_grad(co, tn, yn, dn)
+        assert int(r["status"].item()) == 0
+        assert abs(float(r["loglike"]) - float(want["loglike"])) <= 1e-13 * abs(float(want["loglike"]))
+        for nm in gp.COEFF_NAMES:
+            if want["grads"][nm].numel():
+                assert torch.equal(r["grads"][nm], want["grads"][nm]) or relerr(r["grads"][nm].cpu().numpy(), want["grads"][nm].cpu().numpy()) < 1e-12
