@@ -15,7 +15,7 @@ namespace c2b {
 // or one of the two halves of a segment of a longer series (args.cuh).
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
-  if constexpr (JT > 0 && JT <= 8 && !SOLVE) {
+  if constexpr (JT > 0 && JT <= 16 && !SOLVE) {
     // matmuls: diagonal-affine chunk maps
     constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
@@ -29,7 +29,7 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
     }
     C2B_LAUNCH("gsweep_apply_kernel", stream, gsweep_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
   }
-  if constexpr (JT > 0 && JT <= 8 && SOLVE) {
+  if constexpr (JT > 0 && JT <= 16 && SOLVE) {
     const int phase = a.seg.phase;
     int rc;
     if (a.C > 1 || phase != 0) {
@@ -62,7 +62,7 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
 
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
-  if constexpr (JT > 0 && JT <= 8 && !SOLVE) {
+  if constexpr (JT > 0 && JT <= 16 && !SOLVE) {
     constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
     if (a.C > 1) {
@@ -77,7 +77,7 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     C2B_LAUNCH("rev_finalize_kernel", stream,
                rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   }
-  if constexpr (JT > 0 && JT <= 8 && SOLVE) {
+  if constexpr (JT > 0 && JT <= 16 && SOLVE) {
     const int phase = a.seg.phase;
     int rc;
     if (a.C > 1 || phase != 0) {
@@ -140,11 +140,11 @@ static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_
 
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
-  if (a.seg.phase != 0 && !(JT > 0 && JT <= 8 && SOLVE && a.K == 1)) {
-    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 2, 4, 6 only");
+  if (a.seg.phase != 0 && !(JT > 0 && JT <= 16 && SOLVE && a.K == 1)) {
+    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 2, 4, 6, 16 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 8 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+  if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
     return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
   if (JT > 0 && SOLVE && a.K > 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
@@ -180,11 +180,11 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
 
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
-  if (a.seg.phase != 0 && !(JT > 0 && JT <= 8 && SOLVE && a.K == 1)) {
-    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 2, 4, 6 only");
+  if (a.seg.phase != 0 && !(JT > 0 && JT <= 16 && SOLVE && a.K == 1)) {
+    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 2, 4, 6, 16 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 8 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+  if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
     return launch_sweep_rev_group<JT, SOLVE, LOWER>(a, sb, bc, stream);
   unsigned grid, block;
   size_t smem;

@@ -110,7 +110,7 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
  * run of rows [r0, r1) of the series; the caller passes pointers to the segment's first row (t + r0, U + r0*J, ...) and
  * N = r1 - r0.  The time stamps of the neighbouring rows must be addressable through the same pointer when has_left /
  * has_right say so (t[-1], t[N]): replicate t on every device or keep a one-element halo.  batch must be 1 and the
- * width one of the compiled ones (J in 2, 4, 6, 16; sweeps: J <= 6, K = 1).  Each of the four operators of the
+ * width one of the compiled ones (J in 2, 4, 6, 16; sweeps: K = 1).  Each of the four operators of the
  * log-likelihood + gradient pipeline runs in two calls with the SAME scratch buffer (which holds the tree in between):
  *   phase C2B_SEG_SUMMARISE: summary pass + up-sweep; the segment's summary element (c2b_segment_sizes doubles) is
  *                            written to summary_out.  Exchange the summaries of all segments (all-gather),

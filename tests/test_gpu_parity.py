@@ -121,7 +121,7 @@ def _bigger_case(name, N, K, seed):
 
 
 @pytest.mark.parametrize("chunks", [0, 3, 40, 333])
-@pytest.mark.parametrize("name,K", [("sho_under", 1), ("sum4", 2), ("c2_J6", 1), ("sum2", 3), ("sho4_J8", 1)])
+@pytest.mark.parametrize("name,K", [("sho_under", 1), ("sum4", 2), ("c2_J6", 1), ("sum2", 3), ("sho4_J8", 1), ("c4_J16", 1), ("c4_J16", 5)])
 def test_oracle_chunked_pipeline(env, name, K, chunks):
     """N = 4000: factor -> solve_lower -> reverse ops, against the oracle, for several chunk counts
     (3: one warp block; 40: two warp blocks, exercises the top-level scan; 333: deeper tree)."""

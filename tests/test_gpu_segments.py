@@ -10,7 +10,7 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-@pytest.mark.parametrize("name", ["c2_J6", "sum4", "sho_under"])
+@pytest.mark.parametrize("name", ["c2_J6", "sum4", "sho_under", "c4_J16"])
 @pytest.mark.parametrize("bounds,chunks", [((0, 1700, 5000), 0), ((0, 1, 2000, 4999, 5000), 0), ((0, 40, 2100, 5000), 7),
                                            ((0, 1250, 2500, 3750, 5000), 3)])
 def test_segments_reproduce_the_whole_series(name, bounds, chunks):
