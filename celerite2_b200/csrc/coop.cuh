@@ -39,6 +39,63 @@ C2B_DEV void wsym_add(int lane, int J, const double *R, const double *Cadd, doub
   }
 }
 
+// Compile-time-width versions: the passes over the J*J outputs (two for J = 6) are unrolled with a predicate, each
+// output's 2 J operands are loaded before its multiply-add chain starts, so the passes and the loads overlap.  With
+// one warp per scheduler at the upper tree levels every dependent instruction costs its full latency (r01i profile:
+// 15-17 cycles per instruction, 2 us per level for a 6 x 6 product); this is what bounds the scan.
+template <int J, bool TA, bool TB>
+C2B_DEV void wmm_ct(int lane, const double *A, int lda, const double *B, int ldb, double *out, int ldo) {
+  constexpr int NE = J * J, NP = (NE + 31) / 32;
+  if constexpr (J <= 8) {
+    double a[NP][J], b[NP][J];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const int e = lane + 32 * p;
+      const int i = e < NE ? e / J : 0, j = e < NE ? e % J : 0;
+#pragma unroll
+      for (int k = 0; k < J; ++k) {
+        a[p][k] = TA ? A[k * lda + i] : A[i * lda + k];
+        b[p][k] = TB ? B[j * ldb + k] : B[k * ldb + j];
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const int e = lane + 32 * p;
+      double s    = 0.0;
+#pragma unroll
+      for (int k = 0; k < J; ++k) s = fma(a[p][k], b[p][k], s);
+      if (e < NE) out[(e / J) * ldo + (e % J)] = s;
+    }
+  } else {
+    // wide matrices: one pass at a time (the operands of all passes would not fit the registers), two accumulators
+    for (int p = 0; p < NP; ++p) {
+      const int e = lane + 32 * p;
+      const int i = e < NE ? e / J : 0, j = e < NE ? e % J : 0;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int k = 0; k < J; k += 2) {
+        s0 = fma(TA ? A[k * lda + i] : A[i * lda + k], TB ? B[j * ldb + k] : B[k * ldb + j], s0);
+        if (k + 1 < J) s1 = fma(TA ? A[(k + 1) * lda + i] : A[i * lda + k + 1], TB ? B[j * ldb + k + 1] : B[(k + 1) * ldb + j], s1);
+      }
+      if (e < NE) out[i * ldo + j] = s0 + s1;
+    }
+  }
+}
+
+// out = 0.5 (R + R^T) + Cadd
+template <int J>
+C2B_DEV void wsym_add_ct(int lane, const double *R, const double *Cadd, double *out) {
+  constexpr int NE = J * J, NP = (NE + 31) / 32;
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    const int e = lane + 32 * p;
+    if (e < NE) {
+      const int i = e / J, j = e % J;
+      out[e]      = 0.5 * (R[i * J + j] + R[j * J + i]) + Cadd[e];
+    }
+  }
+}
+
 // Solve Mx X = R in place (Mx: J x J, R: J x NR, both row-major in shared memory; Mx is destroyed) by Gauss-Jordan
 // elimination with partial pivoting, the whole warp working on one system: per pivot step the lanes find the
 // pivot row (shuffle arg-max), swap, scale the pivot row and eliminate it from all other rows, each lane owning
@@ -167,7 +224,7 @@ struct Coop<AffV<JT>> {
   __host__ __device__ static int wsmem(int, int) { return 0; }
   C2B_DEV static void wcombine(int lane, int J, int K, const double *e1, const double *e2, double *out, double *) {
     const int JJ = J * J;
-    wmm<false, false>(lane, J, J, J, e2, J, e1, J, nullptr, 0, out, J);  // M = M2 M1
+    wmm_ct<JT, false, false>(lane, e2, J, e1, J, out, J);  // M = M2 M1
     // b = M2 b1 + b2 : b is J x K with element (j,k) at [j + J*k]
     const double *b1 = e1 + JJ, *b2 = e2 + JJ;
     double *b = out + JJ;
@@ -217,22 +274,22 @@ struct Coop<Cong<JT>> {
   C2B_DEV static void wcombine(int lane, int J, int, const double *e1, const double *e2, double *out, double *sm) {
     const int JJ = J * J;
     double *T = sm, *R = sm + JJ;
-    wmm<false, false>(lane, J, J, J, e1, J, e2, J, nullptr, 0, out, J);     // M = M1 M2
-    wmm<false, false>(lane, J, J, J, e1 + JJ, J, e2, J, nullptr, 0, T, J);  // T = B1 M2
+    wmm_ct<JT, false, false>(lane, e1, J, e2, J, out, J);     // M = M1 M2
+    wmm_ct<JT, false, false>(lane, e1 + JJ, J, e2, J, T, J);  // T = B1 M2
     __syncwarp();
-    wmm<true, false>(lane, J, J, J, e2, J, T, J, nullptr, 0, R, J);  // R = M2^T T
+    wmm_ct<JT, true, false>(lane, e2, J, T, J, R, J);  // R = M2^T T
     __syncwarp();
-    wsym_add(lane, J, R, e2 + JJ, out + JJ);
+    wsym_add_ct<JT>(lane, R, e2 + JJ, out + JJ);
     __syncwarp();
   }
   C2B_DEV static void wapply(int lane, int J, int, const double *e, const double *sin, double *sout, double *sm) {
     const int JJ = J * J;
     double *T = sm, *R = sm + JJ;
-    wmm<false, false>(lane, J, J, J, sin, J, e, J, nullptr, 0, T, J);  // T = G M
+    wmm_ct<JT, false, false>(lane, sin, J, e, J, T, J);  // T = G M
     __syncwarp();
-    wmm<true, false>(lane, J, J, J, e, J, T, J, nullptr, 0, R, J);  // R = M^T T
+    wmm_ct<JT, true, false>(lane, e, J, T, J, R, J);  // R = M^T T
     __syncwarp();
-    wsym_add(lane, J, R, e + JJ, sout);
+    wsym_add_ct<JT>(lane, R, e + JJ, sout);
     __syncwarp();
   }
 };
@@ -258,15 +315,15 @@ struct Coop<Lft<JT>> {
     __syncwarp();
     wsolve_reg<JT, 2 * JT>(lane, MX, R);
     const double *X1 = R, *X2 = R + J;  // leading dimension 2J
-    wmm<false, false>(lane, J, J, J, A2, J, X1, 2 * J, nullptr, 0, out, J);  // A = A2 X1
-    wmm<false, false>(lane, J, J, J, A2, J, X2, 2 * J, nullptr, 0, T2, J);   // T2 = A2 X2
-    wmm<false, false>(lane, J, J, J, Q2, J, X1, 2 * J, nullptr, 0, T3, J);   // T3 = Q2 X1
+    wmm_ct<JT, false, false>(lane, A2, J, X1, 2 * J, out, J);  // A = A2 X1
+    wmm_ct<JT, false, false>(lane, A2, J, X2, 2 * J, T2, J);   // T2 = A2 X2
+    wmm_ct<JT, false, false>(lane, Q2, J, X1, 2 * J, T3, J);   // T3 = Q2 X1
     __syncwarp();
-    wmm<false, true>(lane, J, J, J, T2, J, A2, J, nullptr, 0, RC, J);  // RC = T2 A2^T
-    wmm<true, false>(lane, J, J, J, A1, J, T3, J, nullptr, 0, RQ, J);  // RQ = A1^T T3
+    wmm_ct<JT, false, true>(lane, T2, J, A2, J, RC, J);  // RC = T2 A2^T
+    wmm_ct<JT, true, false>(lane, A1, J, T3, J, RQ, J);  // RQ = A1^T T3
     __syncwarp();
-    wsym_add(lane, J, RC, e2 + JJ, out + JJ);
-    wsym_add(lane, J, RQ, e1 + 2 * JJ, out + 2 * JJ);
+    wsym_add_ct<JT>(lane, RC, e2 + JJ, out + JJ);
+    wsym_add_ct<JT>(lane, RQ, e1 + 2 * JJ, out + 2 * JJ);
     __syncwarp();
   }
   C2B_DEV static void wapply(int lane, int J, int, const double *e, const double *sin, double *sout, double *sm) {
@@ -282,11 +339,11 @@ struct Coop<Lft<JT>> {
     }
     __syncwarp();
     wsolve_reg<JT, JT>(lane, MX, Z);  // Z = (I + X Q)^-1 X
-    wmm<false, false>(lane, J, J, J, A, J, Z, J, nullptr, 0, T, J);
+    wmm_ct<JT, false, false>(lane, A, J, Z, J, T, J);
     __syncwarp();
-    wmm<false, true>(lane, J, J, J, T, J, A, J, nullptr, 0, R, J);
+    wmm_ct<JT, false, true>(lane, T, J, A, J, R, J);
     __syncwarp();
-    wsym_add(lane, J, R, e + JJ, sout);
+    wsym_add_ct<JT>(lane, R, e + JJ, sout);
     __syncwarp();
   }
 };
