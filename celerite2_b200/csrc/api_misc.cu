@@ -195,7 +195,23 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
   g.Fout = F;
   unsigned grid, block;
   launch_shape(pl.C * K, &grid, &block);
-  if (pl.C > 1) {
+  // one right-hand side and a compiled width: the running sums come from the lane-group tile kernels (gsweep.cuh)
+  bool states_done = false;
+  if (K == 1 && !getenv("C2B_NO_GROUP")) {
+    SweepArgs a;
+    memset(&a, 0, sizeof(a));
+    a.N = M; a.batch = 1; a.C = pl.C; a.L = pl.L; a.J = J; a.K = 1; a.tmin = 0; a.tmax = M - 1;
+    a.t = t2; a.c = c; a.B = V; a.A = V; a.Y = Y; a.F = g.H;
+    int rg = C2B_ERR_INVALID_ARGUMENT;
+#define CALL(JT) rg = launch_gm_states<JT, UPPER>(a, sb, stream)
+    C2B_DISPATCH_J_SWEEP(J, CALL)
+#undef CALL
+    if (rg != C2B_OK && rg != C2B_ERR_INVALID_ARGUMENT) return rg;
+    states_done = rg == C2B_OK;
+  }
+  if (states_done) {
+    // fall through to the gather
+  } else if (pl.C > 1) {
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
     C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, true><<<grid, block, 0, stream>>>(g));
@@ -203,7 +219,7 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
     if (rc) return rc;
     g.carry = sb.states;
   }
-  C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, false><<<grid, block, 0, stream>>>(g));
+  if (!states_done) C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, false><<<grid, block, 0, stream>>>(g));
   C2B_LAUNCH("gm_gather_kernel", stream, gm_gather_kernel<UPPER><<<(unsigned)((N * K + 127) / 128), 128, 0, stream>>>(g));
   if (F) {
     C2B_LAUNCH("gm_workspace_kernel", stream, gm_workspace_kernel<UPPER><<<(unsigned)((M * (int64_t)J * K + 127) / 128), 128, 0, stream>>>(g));

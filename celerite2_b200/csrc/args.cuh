@@ -90,6 +90,10 @@ template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream);
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream);
+// running sums H_m (state after every row) of the rectangular products, K = 1: a.t = t2, a.B = V, a.Y = Y, a.F = H (inst_sweep.cu);
+// returns C2B_ERR_INVALID_ARGUMENT without touching anything when the width has no lane-group kernels
+template <int JT, bool UPPER>
+int launch_gm_states(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream);
 // state entering segment `which` of nseg from the segments' summaries; kind: 0 factor, 1 factor_rev (inst_factor.cu),
 // 2 solve_lower, 3 solve_lower_rev (inst_sweep.cu, K = 1)
 template <int JT>

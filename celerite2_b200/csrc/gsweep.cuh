@@ -211,8 +211,11 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
 }
 
 // ---- forward summary, matmuls: diagonal-affine chunk map G -> m o G + b, lane c holding element c ----------------------
+// STORE = false: the chunk's summary (m, b) goes to the leaves.  STORE = true: the walk starts from the carried state and
+// the state AFTER every row is written to a.F (N x J): the running sums H_m of the rectangular products
+// (general_matmul_lower / upper, forward.hpp:285-392).
 // tile buffer: B[R*J] | t[R+2] y[R]
-template <int J, bool LOWER>
+template <int J, bool LOWER, bool STORE = false>
 __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_msummary_kernel(SweepArgs a) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreadsS / G;
@@ -243,6 +246,13 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_msummary_kernel(Swee
   __syncwarp();
   pairs.init(scc + gin * JE, c);
   double Fc = 0.0, mc = 1.0;
+  if (STORE && a.carry && act) {
+    const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
+    Fc                 = a.carry[(b * a.node_stride + leaf) * (int64_t)J + c];
+  }
+  constexpr int dir = LOWER ? 1 : -1;
+  const int64_t nf  = LOWER ? n0 : n1 - 1;
+  double *H         = STORE ? a.F + b * a.N * J : nullptr;
   const int cnt    = (int)(n1 - n0);
   const int ntile  = (cnt + R - 1) / R;
   const int ttrips = warp_max(ntile);
@@ -276,12 +286,13 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_msummary_kernel(Swee
       if (r < rows) {
         mc *= p[r];
         Fc = fma(act ? tb[s * J + cj] : 0.0, tb[oY + s], p[r] * Fc);
+        if (STORE && act) H[(nf + (int64_t)dir * (k * R + r)) * J + c] = Fc;
       }
     }
     __syncwarp();
     issue(k + 2);
   }
-  if (act) {
+  if (!STORE && act) {
     const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
     double *e          = a.leaves + (b * a.node_stride + leaf) * (int64_t)(2 * J);
     e[c]               = mc;

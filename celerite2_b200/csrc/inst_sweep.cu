@@ -220,6 +220,29 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
   return C2B_OK;
 }
 
+template <int JT, bool UPPER>
+int launch_gm_states(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
+  if constexpr (JT > 0 && JT <= 16) {
+    constexpr bool LOWER = !UPPER;
+    constexpr int GP     = kGroupThreadsS / GroupOf<JT>::G;
+    const unsigned grid  = (unsigned)((a.batch * a.C + GP - 1) / GP);
+    if (a.C > 1) {
+      a.leaves      = sb.nodes;
+      a.node_stride = sb.node_stride;
+      C2B_LAUNCH("gsweep_msummary_kernel", stream, (gsweep_msummary_kernel<JT, LOWER, false><<<grid, kGroupThreadsS, 0, stream>>>(a)));
+      int rc = run_scan<DiagV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      if (rc) return rc;
+      a.carry = sb.states;
+    }
+    C2B_LAUNCH("gsweep_states_kernel", stream, (gsweep_msummary_kernel<JT, LOWER, true><<<grid, kGroupThreadsS, 0, stream>>>(a)));
+    return C2B_OK;
+  } else {
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+}
+template int launch_gm_states<C2B_JT, false>(SweepArgs &, const ScanBuffers &, cudaStream_t);
+template int launch_gm_states<C2B_JT, true>(SweepArgs &, const ScanBuffers &, cudaStream_t);
+
 template <int JT>
 int launch_seg_carry_sweep(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream) {
   // solve_lower walks upwards, solve_lower_rev downwards
