@@ -106,13 +106,15 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
     }
     int64_t target = 8192;
     if (J > 0 && cols <= 1) {
-      const int lanes      = J <= 2 ? 2 : (J <= 4 ? 4 : (J <= 8 ? 8 : (J <= 16 ? 16 : 32)));
-      const int64_t groups = (int64_t)sm_count() * 6 * (64 / lanes);
-      if (groups < target) target = groups;
+      // one wave of lane-group CTAs, shared by the series of a batch; the 8192 limit is on the chunks of ONE series
+      // (the depth of its tree), not on the product
+      const int lanes = J <= 2 ? 2 : (J <= 4 ? 4 : (J <= 8 ? 8 : (J <= 16 ? 16 : 32)));
+      target          = (int64_t)sm_count() * 6 * (64 / lanes);
     }
     if (env_target > 0) target = env_target;
     const int64_t have = batch * (cols > 0 ? cols : 1);
     C                  = have >= target ? 1 : target / have;
+    if (C > 8192) C = 8192;
     const int64_t maxC = N / 64;
     if (C > maxC) C = maxC;
   }
