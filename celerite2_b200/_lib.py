@@ -47,6 +47,8 @@ _SIGS["c2b_factor_segment"] = _SIGS["c2b_factor"] + [_segp]
 _SIGS["c2b_factor_rev_segment"] = _SIGS["c2b_factor_rev"] + [_segp]
 _SIGS["c2b_solve_lower_segment"] = [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp, _segp]
 _SIGS["c2b_solve_lower_rev_segment"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp, _segp]
+_SIGS["c2b_solve_upper_segment"] = _SIGS["c2b_solve_lower_segment"]
+_SIGS["c2b_solve_upper_rev_segment"] = _SIGS["c2b_solve_lower_rev_segment"]
 _SIGS["c2b_segment_sizes"] = [_i32, _i32, _i32, ctypes.POINTER(_i64), ctypes.POINTER(_i64)]
 _SIGS["c2b_segment_carry"] = [_i32, _i32, _i32, _i32, _i32, _vp, _vp, _vp]
 for _op in ("solve_lower", "solve_upper", "matmul_lower", "matmul_upper"):

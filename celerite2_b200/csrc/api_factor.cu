@@ -176,7 +176,9 @@ int c2b_segment_sizes(int32_t op, int32_t J, int32_t K, int64_t *summary_doubles
     case C2B_OP_FACTOR: e = 3 * J * J; s = J * J; break;
     case C2B_OP_FACTOR_REV: e = 2 * J * J; s = J * J; break;
     case C2B_OP_SOLVE_LOWER:
-    case C2B_OP_SOLVE_LOWER_REV: e = J * J + J * K; s = J * K; break;
+    case C2B_OP_SOLVE_UPPER:
+    case C2B_OP_SOLVE_LOWER_REV:
+    case C2B_OP_SOLVE_UPPER_REV: e = J * J + J * K; s = J * K; break;
     default: set_error("c2b_segment_sizes: operator %d cannot run as a segment", (int)op); return C2B_ERR_INVALID_ARGUMENT;
   }
   if (summary_doubles) *summary_doubles = e;
@@ -197,8 +199,8 @@ int c2b_segment_carry(int32_t op, int32_t J, int32_t K, int32_t nseg, int32_t wh
 #define CALL(JT) rc = launch_seg_carry_factor<JT>(kind, nseg, which, summaries, state_out, stream)
     C2B_DISPATCH_J_FACTOR(J, CALL)
 #undef CALL
-  } else if (op == C2B_OP_SOLVE_LOWER || op == C2B_OP_SOLVE_LOWER_REV) {
-    const int kind = op == C2B_OP_SOLVE_LOWER ? 2 : 3;
+  } else if (op == C2B_OP_SOLVE_LOWER || op == C2B_OP_SOLVE_LOWER_REV || op == C2B_OP_SOLVE_UPPER || op == C2B_OP_SOLVE_UPPER_REV) {
+    const int kind = op == C2B_OP_SOLVE_LOWER ? 2 : (op == C2B_OP_SOLVE_LOWER_REV ? 3 : (op == C2B_OP_SOLVE_UPPER ? 4 : 5));
 #define CALL(JT) rc = launch_seg_carry_sweep<JT>(kind, nseg, which, summaries, state_out, stream)
     C2B_DISPATCH_J_SWEEP(J, CALL)
 #undef CALL

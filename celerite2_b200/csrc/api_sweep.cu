@@ -207,4 +207,27 @@ int c2b_solve_lower_rev_segment(int64_t N, int32_t J, int32_t K, int64_t batch, 
                                           stream, seg);
 }
 
+int c2b_solve_upper_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                            const double *W, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                            void *stream, const c2b_segment_t *seg) {
+  c2b::OpScope _op("c2b_solve_upper");
+  if (!seg) {
+    c2b::set_error("c2b_solve_upper_segment: seg is NULL");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  return c2b::sweep_entry<true, false>(N, J, K, batch, t, c, U, W, Y, Z, F, flags, scratch, scratch_bytes, stream, seg);
+}
+int c2b_solve_upper_rev_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                                const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                                double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                                void *stream, const c2b_segment_t *seg) {
+  c2b::OpScope _op("c2b_solve_upper_rev");
+  if (!seg) {
+    c2b::set_error("c2b_solve_upper_rev_segment: seg is NULL");
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  return c2b::sweep_rev_entry<true, false>(N, J, K, batch, t, c, U, W, Y, Z, F, bZ, bt, bc, bU, bW, bY, flags, scratch, scratch_bytes,
+                                           stream, seg);
+}
+
 }  // extern "C"

@@ -95,7 +95,7 @@ int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaS
 template <int JT, bool UPPER>
 int launch_gm_states(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream);
 // state entering segment `which` of nseg from the segments' summaries; kind: 0 factor, 1 factor_rev (inst_factor.cu),
-// 2 solve_lower, 3 solve_lower_rev (inst_sweep.cu, K = 1)
+// 2 solve_lower, 3 solve_lower_rev, 4 solve_upper, 5 solve_upper_rev (inst_sweep.cu, K = 1)
 template <int JT>
 int launch_seg_carry_factor(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream);
 template <int JT>

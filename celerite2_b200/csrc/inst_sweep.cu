@@ -245,8 +245,8 @@ template int launch_gm_states<C2B_JT, true>(SweepArgs &, const ScanBuffers &, cu
 
 template <int JT>
 int launch_seg_carry_sweep(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream) {
-  // solve_lower walks upwards, solve_lower_rev downwards
-  return run_seg_carry<AffV<JT>>(JT, 1, nseg, which, kind == 3, summaries, out, stream);
+  // solve_lower (2) and solve_upper_rev (5) walk upwards, solve_lower_rev (3) and solve_upper (4) downwards
+  return run_seg_carry<AffV<JT>>(JT, 1, nseg, which, kind == 3 || kind == 4, summaries, out, stream);
 }
 
 template int launch_seg_carry_sweep<C2B_JT>(int, int, int, const double *, double *, cudaStream_t);

@@ -152,6 +152,15 @@ int c2b_solve_lower_rev_segment(int64_t N, int32_t J, int32_t K, int64_t batch, 
                                 const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
                                 double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
                                 void *stream, const c2b_segment_t *seg);
+/* solve_upper walks downwards: the segments that come earlier are the higher rows; its reverse operator walks upwards and
+ * owes its edge term to the row just ABOVE the segment (add it to the first bt of the upper neighbour). */
+int c2b_solve_upper_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                            const double *W, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
+                            void *stream, const c2b_segment_t *seg);
+int c2b_solve_upper_rev_segment(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
+                                const double *W, const double *Y, const double *Z, const double *F, const double *bZ, double *bt,
+                                double *bc, double *bU, double *bW, double *bY, int32_t flags, void *scratch, size_t scratch_bytes,
+                                void *stream, const c2b_segment_t *seg);
 
 /*
  * LDL^T factorisation.  Replaces celerite2::core::factor, c++/include/celerite2/forward.hpp:69-135

@@ -85,3 +85,79 @@ def test_segment_argument_errors():
     e, s = ctypes.c_int64(), ctypes.c_int64()
     assert lib.c2b_segment_sizes(_lib.OP_IDS["factor"], 6, 1, ctypes.byref(e), ctypes.byref(s)) == 0 and (e.value, s.value) == (108, 36)
     assert lib.c2b_segment_sizes(_lib.OP_IDS["matmul_lower"], 6, 1, ctypes.byref(e), ctypes.byref(s)) != 0
+
+
+@pytest.mark.parametrize("name", ["c2_J6", "sum4"])
+def test_solve_upper_segments(name):
+    """solve_upper walks downwards (earlier segments = higher rows); its reverse operator walks upwards and owes its
+    edge term to the row just above the segment."""
+    import ctypes
+
+    import torch
+
+    import oracle
+    from celerite2_b200 import _lib, segments
+    from celerite2_b200 import workloads as wl
+
+    lib = _lib.lib
+    dev = torch.device("cuda:0")
+    T = lambda x: torch.as_tensor(np.ascontiguousarray(x, dtype=np.float64), device=dev)
+    H = lambda x: x.detach().cpu().numpy()
+    P = oracle.port()
+    N, bounds = 3000, [0, 700, 701, 2200, 3000]
+    t, y, diag = wl.light_curve(N, 41)
+    c, a, U, V = P.get_celerite_matrices(*ALL_KERNELS[name], t, diag)
+    J = U.shape[1]
+    _, d_r, W_r, _ = P.factor(t, c, a, U, V, workspace=False)
+    Y = y[:, None]
+    Z_r, F_r = P.sweep("solve_upper", t, c, U, W_r, Y)
+    bZ = np.cos(Z_r)
+    want = P.sweep_rev("solve_upper", t, c, U, W_r, Y, Z_r, F_r, bZ)
+    tt, cc = T(t), T(c)
+    nseg = len(bounds) - 1
+    flags = _lib.SHARED_T | _lib.SHARED_C
+    segs = []
+    for r0, r1 in zip(bounds[:-1], bounds[1:]):
+        n = r1 - r0
+        s = dict(n=n, r0=r0, t=tt[r0:r1], U=T(U[r0:r1]), W=T(W_r[r0:r1]), Y=T(Y[r0:r1]), Z=torch.empty((n, 1), dtype=torch.float64, device=dev),
+                 F=torch.empty((n, J), dtype=torch.float64, device=dev), bZ=T(bZ[r0:r1]), left=int(r0 > 0), right=int(r1 < N))
+        for nm, shape in (("bt", (n,)), ("bc", (J,)), ("bU", (n, J)), ("bW", (n, J)), ("bY", (n, 1))):
+            s[nm] = torch.empty(shape, dtype=torch.float64, device=dev)
+        s["edge"] = torch.zeros(1, dtype=torch.float64, device=dev)
+        for op in ("solve_upper", "solve_upper_rev"):
+            need = lib.c2b_scratch_bytes(_lib.OP_IDS[op], n, 0, J, 1, 1)
+            s["scr_" + op] = torch.empty(int(need) + 256, dtype=torch.uint8, device=dev)
+        segs.append(s)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def fwd(s, phase, state=None, out=None):
+        seg = _lib.Segment(phase, s["left"], s["right"], 0, None if state is None else state.data_ptr(), None if out is None else out.data_ptr(), None)
+        b = s["scr_solve_upper"]
+        _lib.check(lib.c2b_solve_upper_segment(s["n"], J, 1, 1, s["t"].data_ptr(), cc.data_ptr(), s["U"].data_ptr(), s["W"].data_ptr(),
+                                               s["Y"].data_ptr(), s["Z"].data_ptr(), s["F"].data_ptr(), flags, b.data_ptr(), b.numel(), stream,
+                                               ctypes.byref(seg)))
+
+    def rev(s, phase, state=None, out=None):
+        seg = _lib.Segment(phase, s["left"], s["right"], 0, None if state is None else state.data_ptr(), None if out is None else out.data_ptr(),
+                           s["edge"].data_ptr())
+        b = s["scr_solve_upper_rev"]
+        _lib.check(lib.c2b_solve_upper_rev_segment(s["n"], J, 1, 1, s["t"].data_ptr(), cc.data_ptr(), s["U"].data_ptr(), s["W"].data_ptr(),
+                                                   s["Y"].data_ptr(), s["Z"].data_ptr(), s["F"].data_ptr(), s["bZ"].data_ptr(), s["bt"].data_ptr(),
+                                                   s["bc"].data_ptr(), s["bU"].data_ptr(), s["bW"].data_ptr(), s["bY"].data_ptr(), flags,
+                                                   b.data_ptr(), b.numel(), stream, ctypes.byref(seg)))
+
+    for op, call in (("solve_upper", fwd), ("solve_upper_rev", rev)):
+        es, _ = segments.segment_sizes("solve_lower", J)
+        summ = torch.empty((nseg, es), dtype=torch.float64, device=dev)
+        for i, s in enumerate(segs):
+            call(s, _lib.SEG_SUMMARISE, out=summ[i])
+        for i, s in enumerate(segs):
+            call(s, _lib.SEG_APPLY, state=segments.segment_carry(op, J, summ, i))
+    cat = lambda nm: np.concatenate([H(s[nm]) for s in segs])
+    assert relerr(cat("Z"), Z_r) < TOL and relerr(cat("F"), F_r) < TOL
+    bt = [H(s["bt"]).copy() for s in segs]
+    for i in range(nseg - 1):  # the edge term of segment i belongs to the first row of segment i + 1
+        bt[i + 1][0] += float(H(segs[i]["edge"])[0])
+    assert relerr(np.concatenate(bt), want[0]) < TOL
+    assert relerr(sum(H(s["bc"]) for s in segs), want[1]) < TOL
+    assert relerr(cat("bU"), want[2]) < TOL and relerr(cat("bW"), want[3]) < TOL and relerr(cat("bY"), want[4]) < TOL
