@@ -466,23 +466,50 @@ static __global__ void __launch_bounds__(1024) rev_finalize_kernel(int64_t N, in
     if (tgt >= 0 && tgt < N) bt[b * N + tgt] += bt_edge[b * C + k];
   }
   if (blockIdx.x != 0) return;
-  // bc[j] = sum over chunks: strided partial sums per thread, then a fixed-shape tree
-  __shared__ double sh[32];
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  for (int j = 0; j < J; ++j) {
-    double s = 0.0;
-    for (int64_t q = threadIdx.x; q < C; q += blockDim.x) s += bc_part[(b * C + q) * J + j];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) sh[wid] = s;
+  // bc[j] = sum over chunks, all J at once: thread (w, j) of warp-sized groups... every thread owns one j and a strided
+  // set of chunks (consecutive threads read consecutive doubles of bc_part), then a fixed-shape tree per j
+  // (deterministic).  One pass over the partials and two barriers, instead of J passes.
+  __shared__ double sh[32 * 32];  // [slot][j], slot = thread / J within the first J * (1024 / J) threads
+  const int per = (int)blockDim.x / J;  // threads per j
+  const int j = threadIdx.x % J, slot = threadIdx.x / J;
+  double s = 0.0;
+  if (slot < per) {
+    const double *p = bc_part + b * C * J;
+    for (int64_t q = slot; q < C; q += per) s += p[q * J + j];
+  }
+  // reduce over slots: first within groups of 32 slots through shared memory
+  const int nslot = per;
+  for (int base = 0; base < nslot; base += 32) {
     __syncthreads();
-    if (wid == 0) {
-      double v = lane < nw ? sh[lane] : 0.0;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) bc[b * J + j] = acc_bc ? bc[b * J + j] + v : v;
+    if (slot >= base && slot < base + 32 && slot < per) sh[(slot - base) * 32 + j] = s;
+    __syncthreads();
+    if (base + 32 < nslot || base > 0) {
+      // more than 32 slots: fold this group's 32 values into the first slot's accumulator of the group
+      if (slot == base && slot < per) {
+        double v        = 0.0;
+        const int count = nslot - base < 32 ? nslot - base : 32;
+        for (int x = 0; x < count; ++x) v += sh[x * 32 + j];
+        s = v;
+      }
     }
+  }
+  __syncthreads();
+  if (nslot <= 32) {
+    if (slot == 0) {
+      double v = 0.0;
+      for (int x = 0; x < nslot; ++x) v += sh[x * 32 + j];
+      bc[b * J + j] = acc_bc ? bc[b * J + j] + v : v;
+    }
+  } else {
+    // group leaders (slot = 0, 32, 64, ...) hold the group sums: gather them through shared memory
+    if (slot % 32 == 0 && slot < per) sh[(slot / 32) * 32 + j] = s;
     __syncthreads();
+    if (slot == 0) {
+      double v       = 0.0;
+      const int ngrp = (nslot + 31) / 32;
+      for (int x = 0; x < ngrp; ++x) v += sh[x * 32 + j];
+      bc[b * J + j] = acc_bc ? bc[b * J + j] + v : v;
+    }
   }
 }
 
