@@ -66,6 +66,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
     for (int j = 0; j < J; ++j) Gc[j] = st[j * J + c];
   }
   double bc_acc = 0.0, pend = 0.0;
+  const bool acc = g.acc != 0;
   const int cnt    = (int)(n1 - n0);
   const int ntile  = (cnt + R - 1) / R;
   const int ttrips = warp_max(ntile);
@@ -94,6 +95,8 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;
     const int64_t nt = n1 - 1 - (int64_t)k * R;  // first row of the tile in visiting order
+    double *bat = WRITE ? ba + nt : nullptr, *btt = WRITE ? bt + nt : nullptr;
+    double *bUt = WRITE ? bU + nt * J + cj : nullptr, *bVt = WRITE ? bV + nt * J + cj : nullptr;
     // dt = t_{n-1} - t_n, 0 at n = 0
     pairs.template eval<R, JE>(pb, c, cc, [&](int r) { return tb[oT + R - 1 - r] - tb[oT + R - r]; });
     __syncwarp();
@@ -130,8 +133,8 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       double *xy = xch + (r & 1) * JE;
       if (c < J) xy[c] = y_c;
       if (WRITE && live) {
-        if (c == G - 1) ba[n] = ban;
-        if (act) bV[n * J + c] = bv_c;
+        if (c == G - 1) bat[-r] = ban;
+        if (act) bVt[-r * J] = bv_c;
       }
       __syncwarp();
       double y[J];
@@ -163,7 +166,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       }
       if (WRITE) {
         cbp[r] = cc * bp;  // bp = 0 on rows without a predecessor
-        if (live && act) out_store(bU + n * J + c, nb ? -(xs * p_c) : 0.0, g.acc);
+        if (live && act) out_store(bUt - r * J, nb ? -(xs * p_c) : 0.0, acc);
       }
     }
     if (WRITE) {
@@ -172,7 +175,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRe
       for (int r = 0; r < R; ++r) {
         const double fac = gsum<G>(cbp[r]);
         if (r < rows) {
-          if (c == 0) out_store(bt + (nt - r), pend - fac, g.acc);
+          if (c == 0) out_store(btt - r, pend - fac, acc);
           pend = fac;
         }
       }
