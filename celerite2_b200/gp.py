@@ -85,6 +85,8 @@ class GraphedLogLikelihood:
             self._front = _front(self.coeffs, t, diag, layout)
         with torch.cuda.graph(self.g_back, pool=self.g_front.pool()):
             self.result = _back(self.coeffs, t, y, diag, self._front, layout, False)
+            # [loglike | d/d ar | d/d cr | d/d ac | d/d bc | d/d cc | d/d dc] in one tensor, packed inside the graph
+            self.packed = torch.cat([self.result["loglike"].reshape(1)] + [self.result["grads"][nm].reshape(-1) for nm in COEFF_NAMES])
 
     def replay_front(self):
         self.g_front.replay()
@@ -144,13 +146,7 @@ class HostLogLikelihood:
         self.graph.replay_front()
         main.wait_event(self.y_ready)
         r = self.graph.replay_back()
-        self.out_d[0:1].copy_(r["loglike"].reshape(1))
-        o = 1
-        for nm in COEFF_NAMES:
-            g = r["grads"][nm]
-            self.out_d[o:o + g.numel()].copy_(g.reshape(-1))
-            o += g.numel()
-        self.out_h.copy_(self.out_d, non_blocking=True)
+        self.out_h.copy_(self.graph.packed, non_blocking=True)
         main.synchronize()  # the caller needs the values
         return self.out_h, r["status"]
 
@@ -198,13 +194,7 @@ class HostLogLikelihoodStream:
         sl["graph"].replay_front()
         main.wait_event(sl["y_ready"])
         r = sl["graph"].replay_back()
-        sl["out_d"][0:1].copy_(r["loglike"].reshape(1))
-        o = 1
-        for nm in COEFF_NAMES:
-            g = r["grads"][nm]
-            sl["out_d"][o:o + g.numel()].copy_(g.reshape(-1))
-            o += g.numel()
-        sl["out_h"].copy_(sl["out_d"], non_blocking=True)
+        sl["out_h"].copy_(sl["graph"].packed, non_blocking=True)
         sl["done"].record(main)
         sl["busy"], sl["status"] = True, r["status"]
         self.pending.append(self.next)
