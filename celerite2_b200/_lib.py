@@ -31,6 +31,8 @@ _SIGS = {
     "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
     "c2b_add_inplace": [_i64, _vp, _vp, _vp],
+    "c2b_apply_inverse": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp],
+    "c2b_dot_tril": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp],
     "c2b_solve_lower_noalloc": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp],
 }
 
@@ -55,7 +57,7 @@ for _op in ("solve_lower", "solve_upper", "matmul_lower", "matmul_upper"):
     _SIGS["c2b_" + _op] = [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp]
     _SIGS["c2b_" + _op + "_rev"] = [_i64, _i32, _i32, _i64] + [_vp] * 13 + [_i32, _vp, _sz, _vp]
 
-EXPORTS = sorted(list(_SIGS) + ["c2b_version", "c2b_last_error", "c2b_device_count", "c2b_scratch_bytes", "c2b_set_chunks_per_series",
+EXPORTS = sorted(list(_SIGS) + ["c2b_version", "c2b_last_error", "c2b_device_count", "c2b_scratch_bytes", "c2b_testing_set_chunks_per_series",
                                  "c2b_profile_enable", "c2b_profile_report", "c2b_noalloc_scratch_limit",
                                  "c2b_device_malloc", "c2b_device_free", "c2b_copy_to_device", "c2b_copy_to_host",
                                  "c2b_stream_synchronize"])
@@ -90,8 +92,8 @@ def _load():
     lib.c2b_profile_report.argtypes = []
     lib.c2b_noalloc_scratch_limit.restype = _sz
     lib.c2b_noalloc_scratch_limit.argtypes = []
-    lib.c2b_set_chunks_per_series.restype = None
-    lib.c2b_set_chunks_per_series.argtypes = [_i64]
+    lib.c2b_testing_set_chunks_per_series.restype = None
+    lib.c2b_testing_set_chunks_per_series.argtypes = [_i64]
     return lib
 
 

@@ -19,10 +19,10 @@ LIB = os.path.join(HERE, "libcelerite2_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 # (source, width or None).  The width lists must match C2B_DISPATCH_J_* in csrc/host_common.cuh.
-WIDTHS_SWEEP = [0, 2, 4, 6, 16]
-WIDTHS_FACTOR = [0, 2, 4, 6, 16]
+WIDTHS_SWEEP = [0, 1, 2, 3, 4, 5, 6, 7, 8, 16]
+WIDTHS_FACTOR = [0, 1, 2, 3, 4, 5, 6, 7, 8, 16]
 UNITS = (
-    [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_pipeline.cu", None), ("api_noalloc.cu", None)]
+    [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_noalloc.cu", None)]
     + [("inst_sweep.cu", w) for w in WIDTHS_SWEEP]
     + [("inst_factor.cu", w) for w in WIDTHS_FACTOR]
 )
@@ -33,7 +33,6 @@ FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxe
 _COMMON = ["common.cuh", "monoids.cuh", "coop.cuh", "scan.cuh", "args.cuh", "host_common.cuh"]
 _EXTRA = {
     "api_misc.cu": ["misc.cuh"],
-    "api_pipeline.cu": ["misc.cuh"],
     "inst_sweep.cu": ["sweep.cuh", "group.cuh", "gsweep.cuh"],
     "inst_factor.cu": ["factor.cuh", "group.cuh", "gfactor.cuh", "gfactor_rev.cuh"],
 }
@@ -53,7 +52,10 @@ def _stale(target, deps):
 
 def build(force=False, verbose_ptxas=False):
     os.makedirs(OBJ, exist_ok=True)
-    units = [(u, w) for (u, w) in UNITS if os.path.exists(os.path.join(CSRC, u))]
+    units = list(UNITS)
+    missing = [u for (u, _) in units if not os.path.exists(os.path.join(CSRC, u))]
+    if missing:
+        raise RuntimeError("celerite2_b200.build: listed sources are missing: %s" % ", ".join(sorted(set(missing))))
 
     def objname(u, w):
         return os.path.join(OBJ, u.replace(".cu", "") + ("" if w is None else "_j%d" % w) + ".o")

@@ -2,6 +2,7 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <string>
@@ -78,15 +79,24 @@ int64_t get_chunk_override() {
 // (registers, shared memory).  So the default is 6 CTAs per SM exactly -- a grid that is a multiple of the SM count --
 // and never more than 8192 chunks (scan cost).
 static int sm_count() {
-  static int n = 0;
+  // per device (a process may drive several), lock-free: a race only repeats the query
+  static std::atomic<int> cache[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = cache[dev].load(std::memory_order_relaxed);
   if (n == 0) {
-    int dev = 0, v = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
-      n = v;
-    else
-      n = 148;
+    int v = 0;
+    n = (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0) ? v : 148;
+    cache[dev].store(n, std::memory_order_relaxed);
   }
   return n;
+}
+
+// Developer switch, read from the environment once per process: C2B_NO_GROUP=1 routes the compiled widths to the
+// generic thread-per-chunk kernels (A/B comparisons on the GPU box).  Not part of the ABI.
+bool no_group_kernels() {
+  static const bool v = getenv("C2B_NO_GROUP") != nullptr;
+  return v;
 }
 
 Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
@@ -199,7 +209,7 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
   launch_shape(pl.C * K, &grid, &block);
   // one right-hand side and a compiled width: the running sums come from the lane-group tile kernels (gsweep.cuh)
   bool states_done = false;
-  if (K == 1 && !getenv("C2B_NO_GROUP")) {
+  if (K == 1 && !no_group_kernels()) {
     SweepArgs a;
     memset(&a, 0, sizeof(a));
     a.N = M; a.batch = 1; a.C = pl.C; a.L = pl.L; a.J = J; a.K = 1; a.tmin = 0; a.tmax = M - 1;
@@ -277,7 +287,7 @@ const char *c2b_profile_report(void) {
   return c2b::g_report.c_str();
 }
 
-void c2b_set_chunks_per_series(int64_t chunks) { c2b::g_chunk_override = chunks > 0 ? chunks : 0; }
+void c2b_testing_set_chunks_per_series(int64_t chunks) { c2b::g_chunk_override = chunks > 0 ? chunks : 0; }
 
 size_t c2b_scratch_bytes(int32_t op, int64_t N, int64_t M, int32_t J, int32_t K, int64_t batch) {
   using namespace c2b;

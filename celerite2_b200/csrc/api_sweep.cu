@@ -48,7 +48,7 @@ int segment_setup(const c2b_segment_t *seg, int64_t N, int64_t batch, const void
 template <bool SOLVE, bool LOWER>
 static int sweep_entry(int64_t N, int J, int K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
                        const double *Y, double *Z, double *F, int flags, void *scratch, size_t scratch_bytes, void *stream_,
-                       const c2b_segment_t *seg = nullptr) {
+                       const c2b_segment_t *seg = nullptr, const double *zdiv = nullptr) {
   int rc = check_common(N, J, batch);
   if (rc) return rc;
   C2B_REQUIRE(K >= 1, "K (number of right-hand sides) must be >= 1");
@@ -72,6 +72,7 @@ static int sweep_entry(int64_t N, int J, int K, int64_t batch, const double *t, 
     memset(&a, 0, sizeof(a));
     a.N = N; a.batch = batch; a.C = pl.C; a.L = pl.L; a.J = J; a.tmin = tmin; a.tmax = tmax; a.seg = sg; a.K = K;
     a.t = t; a.c = c; a.Y = Y; a.Z = Z; a.F = F;
+    a.zdiv = SOLVE ? zdiv : nullptr;
     a.A = LOWER ? U : W;
     a.B = LOWER ? W : U;
     a.t_bs = (flags & C2B_SHARED_T) ? 0 : N;
@@ -130,9 +131,44 @@ static int sweep_rev_entry(int64_t N, int J, int K, int64_t batch, const double 
   return rc;
 }
 
+// Z[b][n][k] = Y[b][n][k] * sqrt(d[b][n]): the first half of dot_tril (python/celerite2/numpy.py:100-102)
+static __global__ void __launch_bounds__(256) scale_sqrt_rows_kernel(int64_t total, int64_t NK, int K, int64_t y_bs, const double *d,
+                                                                     const double *Y, double *Z) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t b = i / NK, r = i - b * NK;
+    Z[i]            = Y[b * y_bs + r] * sqrt(d[i / K]);
+  }
+}
+
 }  // namespace c2b
 
 extern "C" {
+
+int c2b_apply_inverse(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                      const double *d, const double *Y, double *Z, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_apply_inverse");
+  C2B_REQUIRE(d != nullptr, "null data pointer");
+  // Z = L^-1 Y with the division by d folded into the store of every row, then Z = L^-T Z in place
+  int rc = c2b::sweep_entry<true, true>(N, J, K, batch, t, c, U, W, Y, Z, nullptr, flags, scratch, scratch_bytes, stream, nullptr, d);
+  if (rc) return rc;
+  return c2b::sweep_entry<true, false>(N, J, K, batch, t, c, U, W, Z, Z, nullptr, flags & ~C2B_SHARED_Y, scratch, scratch_bytes, stream);
+}
+
+int c2b_dot_tril(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                 const double *d, const double *Y, double *Z, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {
+  c2b::OpScope _op("c2b_dot_tril");
+  using namespace c2b;
+  int rc = check_common(N, J, batch);
+  if (rc) return rc;
+  C2B_REQUIRE(K >= 1 && d && Y && Z, "bad arguments");
+  const int64_t NK = N * (int64_t)K, total = batch * NK;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  C2B_LAUNCH("scale_sqrt_rows_kernel", (cudaStream_t)stream,
+             (scale_sqrt_rows_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(total, NK, K, (flags & C2B_SHARED_Y) ? 0 : NK, d, Y, Z)));
+  // z <- L z in place: the sweep keeps the previous INPUT row (internal.hpp:134-141), so aliasing Y and Z is exact
+  return sweep_entry<false, true>(N, J, K, batch, t, c, U, W, Z, Z, nullptr, flags & ~C2B_SHARED_Y, scratch, scratch_bytes, stream);
+}
 
 int c2b_solve_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
                     const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes, void *stream) {

@@ -31,6 +31,8 @@ struct SweepArgs {
   int J, K;
   const double *t, *c, *A, *B, *Y;  // A = "output" vector (dotted with the state), B = "input" vector
   double *Z, *F;
+  const double *zdiv;    // solves only, nullable: the stored result is z / zdiv[n] (the "/ d" between the two sweeps of
+                         // apply_inverse, python/celerite2/numpy.py:94-98, folded into the store); the recursion uses z
   int64_t t_bs, c_bs, y_bs;  // batch strides (0 when shared)
   // scan plumbing
   double *leaves;        // [batch][C][esize]   (summary kernels write here)

@@ -69,6 +69,7 @@ struct Plan {
 };
 Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J);
 int64_t get_chunk_override();
+bool no_group_kernels();
 
 static inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 

@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
   const double *t     = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
   double *Z = a.Z + b * a.N, *F = a.F ? a.F + b * a.N * J : nullptr;
+  const double *zdiv = (SOLVE && a.zdiv) ? a.zdiv + b * a.N : nullptr;
   double *gbuf = stile + gin * GS;
   const GCopy<G> cp{c};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
@@ -103,7 +104,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
         z  = zold + sm;
         rr = y;
       }
-      if (live && c == G - 1) Zt[dir * r] = z;
+      if (live && c == G - 1) Zt[dir * r] = zdiv ? z / zdiv[nf + (int64_t)dir * (k * R + r)] : z;
       Fc = fma(b_c, rr, Fc);
     }
     __syncwarp();
@@ -645,7 +646,7 @@ template <int J>
 __host__ __device__ inline size_t csweep_smem_doubles(int yw) {
   constexpr int R = kTileRows;
   const int tb    = 2 * R * J + ((R + 2 + 1) & ~1) + R * yw;
-  return (size_t)2 * tb + R * J + J;
+  return (size_t)2 * tb + R * J + J + R;
 }
 
 template <int J, bool LOWER, bool SUMMARY>
@@ -663,11 +664,13 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
   const int TB         = oY + R * yw;
   double *pb           = cs_smem + 2 * TB;
   double *csm          = pb + R * J;
+  double *dinv         = csm + J;  // 1 / zdiv of the tile's rows (apply pass of apply_inverse)
   const double *t      = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J;
   const double *Y = a.Y + b * a.y_bs;
   double *Z = a.Z + b * a.N * (int64_t)a.K;
   double *F = (!SUMMARY && a.F) ? a.F + b * a.N * (int64_t)J * a.K : nullptr;
+  const double *zdiv = (!SUMMARY && a.zdiv) ? a.zdiv + b * a.N : nullptr;
   const int64_t leaf = LOWER ? chunk : a.C - 1 - chunk;
   const CtaCopy cp{tid, NT};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
@@ -720,8 +723,9 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
         const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
         pb[i] = exp(csm[j] * dt);  // dt = 0 (propagator 1) at the end of the series
       }
-      __syncthreads();
       const int64_t nt = nf + (int64_t)dir * kt * R;  // first row of the tile in visiting order
+      if (zdiv && tid < rows) dinv[tid] = 1.0 / zdiv[nt + dir * tid];
+      __syncthreads();
       if (have) {
 #pragma unroll 2
         for (int r = 0; r < R; ++r) {
@@ -743,7 +747,7 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
             }
             const double y = basis ? 0.0 : tb[oY + s * yw + (k - kc0)];
             const double z = y - sm;
-            if (!SUMMARY) Z[n * (int64_t)a.K + k] = z;
+            if (!SUMMARY) Z[n * (int64_t)a.K + k] = zdiv ? z * dinv[r] : z;
             lds_row<J>(tb + oB + s * J, bv);
 #pragma unroll
             for (int j = 0; j < J; ++j) Fk[j] = fma(bv[j], z, Fk[j]);
@@ -836,7 +840,7 @@ __global__ void __launch_bounds__(128) csweep_kernel(SweepArgs a) {
       s               = fma(aj, Fk[j], s);
     }
     const double z = y - s;
-    if (!SUMMARY && have) Z[n * (int64_t)a.K + k] = z;
+    if (!SUMMARY && have) Z[n * (int64_t)a.K + k] = a.zdiv ? z / a.zdiv[b * a.N + n] : z;
 #pragma unroll
     for (int j = 0; j < J; ++j) {
       const double bj = __shfl_sync(0xffffffffu, b_l, j);

@@ -9,20 +9,18 @@ namespace c2b {
 // here needs its inst_*.cu object.  Other widths (up to C2B_MAX_J) take the run-time-width path (JT = 0).
 #define C2B_DISPATCH_J_SWEEP(J, CALL)                                                                                                     \
   switch (J) {                                                                                                                            \
+    case 1: CALL(1); break;                                                                                                               \
     case 2: CALL(2); break;                                                                                                               \
+    case 3: CALL(3); break;                                                                                                               \
     case 4: CALL(4); break;                                                                                                               \
+    case 5: CALL(5); break;                                                                                                               \
     case 6: CALL(6); break;                                                                                                               \
+    case 7: CALL(7); break;                                                                                                               \
+    case 8: CALL(8); break;                                                                                                               \
     case 16: CALL(16); break;                                                                                                             \
     default: CALL(0); break;                                                                                                              \
   }
-#define C2B_DISPATCH_J_FACTOR(J, CALL)                                                                                                    \
-  switch (J) {                                                                                                                            \
-    case 2: CALL(2); break;                                                                                                               \
-    case 4: CALL(4); break;                                                                                                               \
-    case 6: CALL(6); break;                                                                                                               \
-    case 16: CALL(16); break;                                                                                                             \
-    default: CALL(0); break;                                                                                                              \
-  }
+#define C2B_DISPATCH_J_FACTOR(J, CALL) C2B_DISPATCH_J_SWEEP(J, CALL)
 
 // Thread-per-unit kernels: few units => small CTAs so that every SM gets some.
 static inline void launch_shape(int64_t units, unsigned *grid, unsigned *block) {

@@ -46,10 +46,10 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
 template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
   if (g.seg.phase != 0 && !(JT > 0 && JT <= 16)) {
-    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !getenv("C2B_NO_GROUP"))) return launch_factor_group<JT>(g, sb, stream);
+  if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !no_group_kernels())) return launch_factor_group<JT>(g, sb, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
@@ -106,10 +106,10 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   if (g.seg.phase != 0 && !(JT > 0 && JT <= 16)) {
-    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !getenv("C2B_NO_GROUP"))) return launch_factor_rev_group<JT>(g, sb, bc, stream);
+  if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !no_group_kernels())) return launch_factor_rev_group<JT>(g, sb, bc, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;

@@ -141,12 +141,12 @@ static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   if (a.seg.phase != 0 && !(JT > 0 && JT <= 16 && SOLVE && a.K == 1)) {
-    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 2, 4, 6, 16 only");
+    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 1..8, 16 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+  if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !no_group_kernels()))
     return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
-  if (JT > 0 && SOLVE && a.K > 1 && !getenv("C2B_NO_GROUP")) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
+  if (JT > 0 && SOLVE && a.K > 1 && !no_group_kernels()) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
@@ -181,10 +181,10 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   if (a.seg.phase != 0 && !(JT > 0 && JT <= 16 && SOLVE && a.K == 1)) {
-    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 2, 4, 6, 16 only");
+    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 1..8, 16 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
-  if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !getenv("C2B_NO_GROUP")))
+  if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !no_group_kernels()))
     return launch_sweep_rev_group<JT, SOLVE, LOWER>(a, sb, bc, stream);
   unsigned grid, block;
   size_t smem;

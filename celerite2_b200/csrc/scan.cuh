@@ -8,6 +8,8 @@
 // above by one CTA per series, the way back down mirrors that.  The state entering the first chunk is zero or
 // a caller-supplied carry (the hand-off point for sharding one series across GPUs).
 #pragma once
+#include <atomic>
+
 #include "coop.cuh"
 
 namespace c2b {
@@ -341,14 +343,14 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
       return C2B_ERR_INVALID_ARGUMENT;
     }
     const unsigned nslices = (unsigned)((K + kb - 1) / kb);
-    static bool attr_done[64] = {};  // per instantiation and device
+    static std::atomic<bool> attr_done[64];  // per instantiation and device; a race only repeats the (idempotent) calls
     int dev = 0;
     C2B_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_done[dev]) {
+    if (dev < 0 || dev >= 64 || !attr_done[dev].load(std::memory_order_acquire)) {
       C2B_CUDA(cudaFuncSetAttribute(scan_block<Mon, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
       C2B_CUDA(cudaFuncSetAttribute(scan_block<Mon, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
       C2B_CUDA(cudaFuncSetAttribute(scan_block<Mon, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-      if (dev >= 0 && dev < 64) attr_done[dev] = true;
+      if (dev >= 0 && dev < 64) attr_done[dev].store(true, std::memory_order_release);
     }
     const int top = lv.nlev - 1;
     int bases[kMaxLevels], nb = 0;
@@ -377,7 +379,7 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
     return C2B_OK;
   } else {
   if (mode != 0) {
-    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
   const int threads  = 128;  // 4 warps
@@ -446,7 +448,7 @@ static inline int run_seg_carry(int J, int K, int nseg, int which, bool descendi
     C2B_LAUNCH("seg_carry_kernel", stream, (seg_carry_kernel<Mon><<<1, 32, smem, stream>>>(J, K, nseg, which, descending, summaries, out)));
     return C2B_OK;
   } else {
-    set_error("segments of a longer series need a compiled width (J in 2, 4, 6, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
 }

@@ -33,7 +33,8 @@ struct SweepRow {
 
 template <int JT, bool SOLVE, bool LOWER, bool WRITE>
 C2B_DEV void sweep_rows(int J, int K, int64_t N, int64_t n0, int64_t n1, const double *t, const double *cj, const unsigned *dup,
-                        const double *A, const double *B, const double *Ycol, double *Zcol, double *Fcol, double *G, double *smem) {
+                        const double *A, const double *B, const double *Ycol, double *Zcol, double *Fcol, double *G, double *smem,
+                        const double *zdiv = nullptr) {
   constexpr int MJ = Width<JT>::MAXJ;
   RowPipe<(JT > 0), SweepRow<JT>::ROWD, kSweepSlots> rp;
   rp.init(smem);
@@ -90,7 +91,7 @@ C2B_DEV void sweep_rows(int J, int K, int64_t N, int64_t n0, int64_t n1, const d
       z = (WRITE ? rp.get(3) : 0.0) + s;
       r = y;
     }
-    if (WRITE) Zcol[n * (int64_t)K] = z;
+    if (WRITE) Zcol[n * (int64_t)K] = (SOLVE && zdiv) ? z / zdiv[n] : z;
     C2B_UNROLL_J
     for (int j = 0; j < J; ++j) G[j] = fma(rp.get(4 + MJ + j), r, G[j]);
     rp.release();
@@ -134,7 +135,8 @@ __global__ void sweep_apply_kernel(SweepArgs a) {
   }
   const int64_t NJ = a.N * J, NK = a.N * a.K;
   sweep_rows<JT, SOLVE, LOWER, true>(J, a.K, a.N, n0, n1, t, cj, dup, a.A + b * NJ, a.B + b * NJ, a.Y + b * a.y_bs + col,
-                                     a.Z + b * NK + col, a.F ? a.F + b * NK * J + (int64_t)J * col : nullptr, G, c2b_ring);
+                                     a.Z + b * NK + col, a.F ? a.F + b * NK * J + (int64_t)J * col : nullptr, G, c2b_ring,
+                                     a.zdiv ? a.zdiv + b * a.N : nullptr);
 }
 
 // ---- summary: thread per (series, chunk, column'), column' in [0, J+K) for solves, [0, K) for matmuls ---------

@@ -22,14 +22,23 @@ COEFF_NAMES = ("ar", "cr", "ac", "bc", "cc", "dc")
 def log_likelihood(coeffs, t, y, diag, layout="blocked"):
     """coeffs: six CUDA tensors (Jr,)/(Jc,) or (B,Jr)/(B,Jc); t (N) or (B,N); y (N) or (B,N); diag (N) or (B,N).
     -> (loglike (B,) or scalar tensor, status)"""
+    r = _back_value(y, diag, _front_value(coeffs, t, diag, layout))
+    return r["loglike"], r["status"]
+
+
+def _front_value(coeffs, t, diag, layout):
+    """value only: assembly + in-place factorisation without the workspace (numpy.py:66-87)"""
     c, a, U, V = ops.get_celerite_matrices(*coeffs, t, diag, layout=layout)
     d, W, _, status = ops.factor(t, c, a, U, V, d=a, W=V, workspace=False)
-    Y = y.unsqueeze(-1)
-    Z, _ = ops.solve_lower(t, c, U, W, Y)
+    return t, c, U, W, d, status
+
+
+def _back_value(y, diag, front):
+    t, c, U, W, d, status = front
+    Z, _ = ops.solve_lower(t, c, U, W, y.unsqueeze(-1))
     out, _, _ = ops.norm_logdet(d, Z.squeeze(-1))
-    N = diag.shape[-1]
-    ll = -0.5 * (out[..., 0] + out[..., 1] + N * math.log(2 * math.pi))
-    return ll, status
+    ll = -0.5 * (out[..., 0] + out[..., 1] + diag.shape[-1] * math.log(2 * math.pi))
+    return dict(loglike=ll, status=status)
 
 
 def _front(coeffs, t, diag, layout):
@@ -50,6 +59,8 @@ def _back(coeffs, t, y, diag, front, layout, want_data_grads):
     _, _, ba, _, bV = ops.factor_rev(t, c, a, U, V, d, W, S, bd, bW, accumulate_into=(bt, bc, bU))
     g = ops.get_celerite_matrices_rev(*coeffs, t, bc, ba, bU, bV, b_x=bt, layout=layout, want_diag=want_data_grads)
     res = dict(loglike=ll, status=status, grads=dict(zip(COEFF_NAMES, g[:6])))
+    # the operator-level outputs (views, nothing copied): what the parity checks compare with the reference's arrays
+    res["raw"] = dict(c=c, a=a, U=U, V=V, d=d, W=W, S=S, Z=Z, F=F, bt=bt, bc=bc, ba=ba, bU=bU, bV=bV, bY=bY)
     if want_data_grads:
         res["grads"].update(t=g[6], y=bY.squeeze(-1), diag=g[7])
     return res
@@ -72,21 +83,34 @@ class GraphedLogLikelihood:
     The results live in fixed tensors that every replay overwrites.
     """
 
-    def __init__(self, coeffs, t, y, diag, layout="blocked", warmup=2):
+    def __init__(self, coeffs, t, y, diag, layout="blocked", warmup=2, grad=True):
         self.coeffs, self.t, self.y, self.diag = list(coeffs), t, y, diag
+        self.grad = grad
+        # The graphs hold the scan scratch by address: this object owns it (ops.scratch_owner), so no later call, of
+        # any size, on any stream, can replace or release memory a replay still writes to.
+        self._scratch = {}
         side = torch.cuda.Stream(device=t.device)
         side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):  # warm-up off the capturing stream: scratch buffers, function attributes
-            for _ in range(warmup):
-                log_likelihood_and_grad(self.coeffs, t, y, diag, layout=layout)
-        torch.cuda.current_stream().wait_stream(side)
-        self.g_front, self.g_back = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.g_front):
-            self._front = _front(self.coeffs, t, diag, layout)
-        with torch.cuda.graph(self.g_back, pool=self.g_front.pool()):
-            self.result = _back(self.coeffs, t, y, diag, self._front, layout, False)
-            # [loglike | d/d ar | d/d cr | d/d ac | d/d bc | d/d cc | d/d dc] in one tensor, packed inside the graph
-            self.packed = torch.cat([self.result["loglike"].reshape(1)] + [self.result["grads"][nm].reshape(-1) for nm in COEFF_NAMES])
+        with ops.scratch_owner(self._scratch):
+            with torch.cuda.stream(side):  # warm-up off the capturing stream: scratch buffers, function attributes
+                for _ in range(warmup):
+                    if grad:
+                        log_likelihood_and_grad(self.coeffs, t, y, diag, layout=layout)
+                    else:
+                        _back_value(y, diag, _front_value(self.coeffs, t, diag, layout))
+            torch.cuda.current_stream().wait_stream(side)
+            self.g_front, self.g_back = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g_front):
+                self._front = _front(self.coeffs, t, diag, layout) if grad else _front_value(self.coeffs, t, diag, layout)
+            with torch.cuda.graph(self.g_back, pool=self.g_front.pool()):
+                if grad:
+                    self.result = _back(self.coeffs, t, y, diag, self._front, layout, False)
+                    # [loglike | d/d ar | d/d cr | d/d ac | d/d bc | d/d cc | d/d dc] in one tensor (series-major blocks
+                    # for a batch: all log-likelihoods, then all d/d ar, ...), packed inside the graph
+                    self.packed = torch.cat([self.result["loglike"].reshape(-1)] + [self.result["grads"][nm].reshape(-1) for nm in COEFF_NAMES])
+                else:
+                    self.result = _back_value(y, diag, self._front)
+                    self.packed = self.result["loglike"].reshape(-1)
 
     def replay_front(self):
         self.g_front.replay()
@@ -114,17 +138,23 @@ class HostLogLikelihood:
     where y is first read (solve_lower), so its transfer overlaps the assembly and the factorisation.
     """
 
-    def __init__(self, N, coeff_shapes, device):
+    def __init__(self, N, coeff_shapes, device, batch=None, shared_ty=False, grad=True):
+        """batch: number of independent series (None = one series, the reference's call).  shared_ty: the series of a batch
+        share t and y (hyper-parameter samples on one data set).  grad=False: log-likelihood only."""
         self.dev = device
+        self.grad = grad
         f8 = dict(dtype=torch.float64, device=device)
-        self.t, self.y, self.diag = (torch.empty(N, **f8) for _ in range(3))
+        lead = () if batch is None else (int(batch),)
+        ty = () if (batch is None or shared_ty) else lead
+        self.t, self.y = torch.empty(ty + (N,), **f8), torch.empty(ty + (N,), **f8)
+        self.diag = torch.empty(lead + (N,), **f8)
         self.co = [torch.empty(tuple(sh), **f8) for sh in coeff_shapes]
-        self.n_out = 1 + sum(v.numel() for v in self.co)
-        self.out_d = torch.empty(self.n_out, **f8)
+        nb = 1 if batch is None else int(batch)
+        self.n_out = nb + (sum(v.numel() for v in self.co) if grad else 0)
         self.out_h = torch.empty(self.n_out, dtype=torch.float64).pin_memory()
         self.side = torch.cuda.Stream(device=device)
         self.y_ready = torch.cuda.Event()
-        self.h2d_bytes = 8 * (3 * N + sum(v.numel() for v in self.co))
+        self.h2d_bytes = 8 * (self.t.numel() + self.y.numel() + self.diag.numel() + sum(v.numel() for v in self.co))
         self.d2h_bytes = 8 * self.n_out
         self.graph = None  # captured at the first call (the staging buffers then hold real data)
 
@@ -142,7 +172,7 @@ class HostLogLikelihood:
             self.y_ready.record(self.side)
         if self.graph is None:
             main.wait_event(self.y_ready)
-            self.graph = GraphedLogLikelihood(self.co, self.t, self.y, self.diag)
+            self.graph = GraphedLogLikelihood(self.co, self.t, self.y, self.diag, grad=self.grad)
         self.graph.replay_front()
         main.wait_event(self.y_ready)
         r = self.graph.replay_back()

@@ -6,12 +6,35 @@ python/celerite2/definitions.json); a leading batch dimension on the per-series 
 kernels.  Shapes: t (N) or (B,N); c (J) or (B,J); a,d (..,N); U,V,W (..,N,J); Y,Z (..,N,K); S (..,N,J,J)
 (S[n] is the reference's row reshaped, i.e. the TRANSPOSE of the column-major matrix); F (..,N,J*K) flat.
 """
+import contextlib
+import threading
+
 import torch
 
 from . import _lib
 from ._lib import SHARED_C, SHARED_T, SHARED_Y, check, lib
 
+# ---- scan scratch -------------------------------------------------------------------------------------------
+# Eager calls share one buffer per (device, stream): calls on one stream are ordered, calls on different streams must
+# not share scratch.  A buffer that was in use while a stream was capturing is baked into a CUDA graph by address and
+# is therefore never released (it moves to _retired when a larger one replaces it).  Pipelines that are captured and
+# replayed (gp.GraphedLogLikelihood) own their scratch outright: `with scratch_owner(obj_dict):` routes every request
+# made inside the block to that dictionary, which lives as long as the object that holds the graphs.
 _scratch = {}
+_retired = []
+_captured = set()
+_tls = threading.local()
+
+
+@contextlib.contextmanager
+def scratch_owner(store):
+    """Route the scratch requests of the calls made inside the block to `store` (a dict owned by the caller)."""
+    prev = getattr(_tls, "store", None)
+    _tls.store = store
+    try:
+        yield store
+    finally:
+        _tls.store = prev
 
 
 def _ptr(x):
@@ -22,15 +45,32 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
+def _scratch_buffer(tag, need, device):
+    """-> uint8 tensor of at least `need` bytes for (tag, device, current stream), owned by the active store"""
+    own = getattr(_tls, "store", None)
+    store = _scratch if own is None else own
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    key = (tag, idx) if own is not None else (tag, idx, torch.cuda.current_stream(device).cuda_stream)
+    buf = store.get(key)
+    capturing = torch.cuda.is_current_stream_capturing()
+    if buf is None or buf.numel() < need:
+        if buf is not None and own is not None:
+            own.setdefault("retired", []).append(buf)  # an earlier capture of the owner may hold its address
+        elif buf is not None and key in _captured:
+            _retired.append(buf)  # a graph the caller captured holds its address
+        buf = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
+        store[key] = buf
+        _captured.discard(key)
+    if capturing and own is None:
+        _captured.add(key)
+    return buf
+
+
 def _get_scratch(op, N, M, J, K, batch, device):
     need = lib.c2b_scratch_bytes(_lib.OP_IDS[op], N, M, J, K, batch)
     if need == 0:
         return None, 0
-    key = (device.index if device.index is not None else torch.cuda.current_device())
-    buf = _scratch.get(key)
-    if buf is None or buf.numel() < need:
-        buf = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, device=device)
-        _scratch[key] = buf
+    buf = _scratch_buffer("scan", need, device)
     return buf.data_ptr(), buf.numel()
 
 
@@ -64,12 +104,13 @@ def _flags(batch, t, c, Y=None):
 
 def set_chunks_per_series(chunks):
     """Force the number of chunks each series is cut into (0 = heuristic).  Testing / tuning knob."""
-    lib.c2b_set_chunks_per_series(int(chunks))
+    lib.c2b_testing_set_chunks_per_series(int(chunks))
 
 
 # ---- assembly ------------------------------------------------------------------------------------------------
-def get_celerite_matrices(ar, cr, ac, bc, cc, dc, x, diag, layout="blocked"):
-    """-> (c, a, U, V).  Coefficient vectors (Jr,)/(Jc,) or (B,Jr)/(B,Jc); x (N) or (B,N); diag (N) or (B,N)."""
+def get_celerite_matrices(ar, cr, ac, bc, cc, dc, x, diag, layout="blocked", out=None):
+    """-> (c, a, U, V).  Coefficient vectors (Jr,)/(Jc,) or (B,Jr)/(B,Jc); x (N) or (B,N); diag (N) or (B,N).
+    out = (c, a, U, V): write into these tensors instead of fresh ones."""
     ar, cr, ac, bc, cc, dc, x, diag = [_f64(v, n) for v, n in zip((ar, cr, ac, bc, cc, dc, x, diag), "ar cr ac bc cc dc x diag".split())]
     batch = diag.shape[0] if diag.dim() == 2 else 1
     N = diag.shape[-1]
@@ -78,10 +119,13 @@ def get_celerite_matrices(ar, cr, ac, bc, cc, dc, x, diag, layout="blocked"):
     flags = (SHARED_T if x.dim() == 1 else 0) | (SHARED_C if ar.dim() == 1 and ac.dim() == 1 else 0)
     lead = (batch,) if diag.dim() == 2 else ()
     dev = diag.device
-    c = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
-    a = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
-    U = torch.empty(lead + (N, J), dtype=torch.float64, device=dev)
-    V = torch.empty(lead + (N, J), dtype=torch.float64, device=dev)
+    if out is not None:
+        c, a, U, V = out
+    else:
+        c = torch.empty(lead + (J,), dtype=torch.float64, device=dev)
+        a = torch.empty(lead + (N,), dtype=torch.float64, device=dev)
+        U = torch.empty(lead + (N, J), dtype=torch.float64, device=dev)
+        V = torch.empty(lead + (N, J), dtype=torch.float64, device=dev)
     check(lib.c2b_get_celerite_matrices({"blocked": 0, "interleaved": 1}[layout], N, Jr, Jc, batch, _ptr(ar), _ptr(cr), _ptr(ac),
                                         _ptr(bc), _ptr(cc), _ptr(dc), _ptr(x), _ptr(diag), _ptr(c), _ptr(a), _ptr(U), _ptr(V), flags,
                                         _stream()))
@@ -190,6 +234,29 @@ def matmul_upper(t, c, U, V, Y, Z=None, workspace=False):
     return _sweep("matmul_upper", t, c, U, V, Y, Z, workspace)
 
 
+def _composite(name, scratch_op, t, c, U, W, d, Y, Z):
+    t, c, U, W, d, Y = [_f64(v, n) for v, n in zip((t, c, U, W, d, Y), "tcUWdY")]
+    batch, N, J = _batch_of(U)
+    K = Y.shape[-1]
+    if Z is None:
+        Z = torch.empty(U.shape[:-1] + (K,), dtype=torch.float64, device=U.device)
+    sp, sb = _get_scratch(scratch_op, N, 0, J, K, batch, U.device)
+    check(getattr(lib, name)(N, J, K, batch, _ptr(t), _ptr(c), _ptr(U), _ptr(W), _ptr(d), _ptr(Y), _ptr(Z), _flags(batch, t, c, Y), sp, sb,
+                             _stream()))
+    return Z
+
+
+def apply_inverse(t, c, U, W, d, Y, Z=None):
+    """Z = K^-1 Y: solve_lower, division by d (folded into the first sweep's store), solve_upper
+    (python/celerite2/numpy.py:94-98).  Pass Z=Y for the in-place form."""
+    return _composite("c2b_apply_inverse", "solve_lower", t, c, U, W, d, Y, Z)
+
+
+def dot_tril(t, c, U, W, d, Y, Z=None):
+    """Z = L (sqrt(d) o Y) (python/celerite2/numpy.py:100-102).  Pass Z=Y for the in-place form."""
+    return _composite("c2b_dot_tril", "matmul_lower", t, c, U, W, d, Y, Z)
+
+
 def _sweep_rev(op, t, c, U, W, Y, Z, F, bZ):
     t, c, U, W, Y, Z, F, bZ = [_f64(v, "arg") for v in (t, c, U, W, Y, Z, F, bZ)]
     batch, N, J = _batch_of(U)
@@ -256,13 +323,7 @@ def norm_logdet(d, z, want_grad=False):
     out = torch.empty(d.shape[:-1] + (2,), dtype=torch.float64, device=dev)
     bz = torch.empty_like(z) if want_grad else None
     bd = torch.empty_like(d) if want_grad else None
-    need = 256 * 1024
-    key = ("red", dev.index)
-    buf = _scratch.get(key)
-    need = max(need, batch * 592 * 16 + 256)
-    if buf is None or buf.numel() < need:
-        buf = torch.empty(need, dtype=torch.uint8, device=dev)
-        _scratch[key] = buf
+    buf = _scratch_buffer("red", max(256 * 1024, batch * 592 * 16 + 256), dev)
     check(lib.c2b_norm_logdet(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(bz), _ptr(bd), buf.data_ptr(), buf.numel(), _stream()))
     return out, bz, bd
 

@@ -65,6 +65,18 @@ class SeriesSegment:
         self.J = self.U.shape[1]
         self._scratch = {}
         self._edge = {}
+        self._alloc = {}
+
+    def reassemble(self):
+        """a/U/V again from the current contents of coeffs, t, diag (new data in the same buffers)"""
+        ops.get_celerite_matrices(*self.coeffs, self.t, self.diag, out=(self.c, self.a, self.U, self.V))
+
+    def _once(self, key, make):
+        """outputs and summaries are allocated at the first evaluation and reused by every later one"""
+        v = self._alloc.get(key)
+        if v is None:
+            v = self._alloc[key] = make()
+        return v
 
     # -- plumbing --------------------------------------------------------------------------------------------------
     def _scr(self, op):
@@ -85,9 +97,9 @@ class SeriesSegment:
     def _factor(self, phase, state_in=None):
         n, J = self.n, self.J
         if phase == _lib.SEG_SUMMARISE:
-            self.d, self.W, self.S = self._new(n), self._new(n, J), self._new(n, J, J)
-            self.status = torch.zeros(1, dtype=torch.int64, device=self.dev)
-            out = self._new(segment_sizes("factor", J)[0])
+            self.d, self.W, self.S, self.status = self._once("factor", lambda: (
+                self._new(n), self._new(n, J), self._new(n, J, J), torch.zeros(1, dtype=torch.int64, device=self.dev)))
+            out = self._once("factor_sum", lambda: self._new(segment_sizes("factor", J)[0]))
         else:
             out = None
         sp, sb = self._scr("factor")
@@ -108,8 +120,8 @@ class SeriesSegment:
         n, J = self.n, self.J
         if phase == _lib.SEG_SUMMARISE:
             self.Y = self.y.unsqueeze(-1)
-            self.Z, self.F = self._new(n, 1), self._new(n, J)
-            out = self._new(segment_sizes("solve_lower", J)[0])
+            self.Z, self.F = self._once("solve", lambda: (self._new(n, 1), self._new(n, J)))
+            out = self._once("solve_sum", lambda: self._new(segment_sizes("solve_lower", J)[0]))
         else:
             out = None
         sp, sb = self._scr("solve_lower")
@@ -133,9 +145,10 @@ class SeriesSegment:
     def _solve_rev(self, phase, state_in=None):
         n, J = self.n, self.J
         if phase == _lib.SEG_SUMMARISE:
-            self.bt, self.bc, self.bU, self.bW, self.bY = self._new(n), self._new(J), self._new(n, J), self._new(n, J), self._new(n, 1)
-            self._edge["solve_lower_rev"] = torch.zeros(1, dtype=torch.float64, device=self.dev)
-            out = self._new(segment_sizes("solve_lower_rev", J)[0])
+            self.bt, self.bc, self.bU, self.bW, self.bY = self._once("solve_rev", lambda: (
+                self._new(n), self._new(J), self._new(n, J), self._new(n, J), self._new(n, 1)))
+            self._edge["solve_lower_rev"] = self._once("solve_rev_edge", lambda: torch.zeros(1, dtype=torch.float64, device=self.dev))
+            out = self._once("solve_rev_sum", lambda: self._new(segment_sizes("solve_lower_rev", J)[0]))
         else:
             out = None
         sp, sb = self._scr("solve_lower_rev")
@@ -156,9 +169,9 @@ class SeriesSegment:
     def _factor_rev(self, phase, state_in=None):
         n, J = self.n, self.J
         if phase == _lib.SEG_SUMMARISE:
-            self.ba, self.bV = self._new(n), self._new(n, J)
-            self._edge["factor_rev"] = torch.zeros(1, dtype=torch.float64, device=self.dev)
-            out = self._new(segment_sizes("factor_rev", J)[0])
+            self.ba, self.bV = self._once("factor_rev", lambda: (self._new(n), self._new(n, J)))
+            self._edge["factor_rev"] = self._once("factor_rev_edge", lambda: torch.zeros(1, dtype=torch.float64, device=self.dev))
+            out = self._once("factor_rev_sum", lambda: self._new(segment_sizes("factor_rev", J)[0]))
         else:
             out = None
         sp, sb = self._scr("factor_rev")
@@ -240,3 +253,66 @@ def loglike_and_grad_distributed(coeffs, t_full, y_seg, diag_seg, r0, r1, group=
     N = t_full.shape[0]
     ll = -0.5 * (pack[0] + pack[1] + N * math.log(2 * math.pi))
     return dict(loglike=ll, status=pack[-1].to(torch.int64), grads=_split_grads(pack[2:-1], coeffs))
+
+
+class SplitSeries:
+    """Rank-resident evaluator of ONE series split over the ranks of a torch.distributed group:
+    the segment's buffers, scratch and exchange buffers are allocated once; `step()` re-evaluates the log-likelihood and
+    its gradient from the current contents of `coeffs`, `t_full`, `y`, `diag` (write new data into them between steps).
+
+    Per operator: summarise -> all_gather of one summary per rank -> device-side fold into the state entering this rank
+    (c2b_segment_carry) -> apply.  One all_reduce at the end sums the partial log-determinant, chi^2 and coefficient
+    gradients and carries, in a slot per rank, the bt term every segment owes the last row of its left neighbour
+    (internal.hpp:226-245, the `bt[n-1] +=` of the row at a segment's lower edge), so that the gradient with respect to the
+    time stamps is complete across segment boundaries as well.
+
+    packed = [sum log d, chi^2, d/d ar .. d/d dc, status] after the reduction, identical on every rank.
+    """
+
+    def __init__(self, coeffs, t_full, y_seg, diag_seg, r0, r1, group=None):
+        import torch.distributed as dist
+
+        self.dist, self.group = dist, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.coeffs, self.t_full, self.y, self.diag = list(coeffs), t_full, y_seg, diag_seg
+        self.seg = SeriesSegment(self.coeffs, t_full, y_seg, diag_seg, r0, r1)
+        self.y, self.diag = self.seg.y, self.seg.diag  # the buffers the segment reads (contiguous)
+        self.N = t_full.shape[0]
+        J = self.seg.J
+        dev = t_full.device
+        self._gather = {op: torch.empty((self.world, segment_sizes(op, J)[0]), dtype=torch.float64, device=dev) for op, _, _ in _STEPS}
+        self._state = {op: torch.empty(segment_sizes(op, J)[1], dtype=torch.float64, device=dev) for op, _, _ in _STEPS}
+        ncoef = sum(v.numel() for v in self.coeffs)
+        self.n_out = 2 + ncoef + 1
+        self.packed = torch.zeros(2 + ncoef + self.world + 1, dtype=torch.float64, device=dev)
+        self._first = True
+
+    def step(self):
+        seg, dist = self.seg, self.dist
+        if not self._first:
+            seg.reassemble()
+        self._first = False
+        red = None
+        for op, summarise, apply in _STEPS:
+            mine = getattr(seg, summarise)()
+            buf = self._gather[op]
+            dist.all_gather_into_tensor(buf, mine, group=self.group)
+            st = self._state[op]
+            check(lib.c2b_segment_carry(_OPS[op], seg.J, 1, self.world, self.rank, _ptr(buf), _ptr(st), _stream()))
+            getattr(seg, apply)(st)
+            if op == "solve_lower":
+                red = seg.reductions()
+        flat = seg.coefficient_gradients()
+        p = self.packed
+        nc = flat.numel()
+        p[0:2] = red.reshape(-1)
+        p[2:2 + nc] = flat
+        p[2 + nc:2 + nc + self.world] = 0.0
+        p[2 + nc + self.rank] = seg.edge_terms()[0]
+        p[-1] = seg.status[0].to(torch.float64)
+        dist.all_reduce(p[:-1], op=dist.ReduceOp.SUM, group=self.group)
+        dist.all_reduce(p[-1:], op=dist.ReduceOp.MAX, group=self.group)
+        if self.rank + 1 < self.world:  # the term the right neighbour owes my last row
+            seg.bt[-1] += p[2 + nc + self.rank + 1]
+        ll = -0.5 * (p[0] + p[1] + self.N * math.log(2 * math.pi))
+        return dict(loglike=ll, status=p[-1].to(torch.int64), grads=_split_grads(p[2:2 + nc], self.coeffs))

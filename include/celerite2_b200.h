@@ -75,7 +75,7 @@ size_t c2b_scratch_bytes(int32_t op, int64_t N, int64_t M, int32_t J, int32_t K,
 void c2b_profile_enable(int32_t on);
 const char *c2b_profile_report(void);
 /* Override the chunk planner (testing / tuning): chunks per series; 0 restores the heuristic. */
-void c2b_set_chunks_per_series(int64_t chunks);
+void c2b_testing_set_chunks_per_series(int64_t chunks);
 
 /*
  * a/U/V (and c) assembly from the kernel coefficients.
@@ -110,7 +110,7 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
  * run of rows [r0, r1) of the series; the caller passes pointers to the segment's first row (t + r0, U + r0*J, ...) and
  * N = r1 - r0.  The time stamps of the neighbouring rows must be addressable through the same pointer when has_left /
  * has_right say so (t[-1], t[N]): replicate t on every device or keep a one-element halo.  batch must be 1 and the
- * width one of the compiled ones (J in 2, 4, 6, 16; sweeps: K = 1).  Each of the four operators of the
+ * width one of the compiled ones (J in 1..8, 16; sweeps: K = 1).  Each of the four operators of the
  * log-likelihood + gradient pipeline runs in two calls with the SAME scratch buffer (which holds the tree in between):
  *   phase C2B_SEG_SUMMARISE: summary pass + up-sweep; the segment's summary element (c2b_segment_sizes doubles) is
  *                            written to summary_out.  Exchange the summaries of all segments (all-gather),
@@ -206,6 +206,21 @@ int c2b_matmul_lower(int64_t N, int32_t J, int32_t K, int64_t batch, const doubl
 int c2b_matmul_upper(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U,
                      const double *V, const double *Y, double *Z, double *F, int32_t flags, void *scratch, size_t scratch_bytes,
                      void *stream);
+
+/*
+ * The two compositions the reference's GP object makes of these operators, python/celerite2/numpy.py:94-102
+ * (SURVEY 8a15), as single calls so that the element-wise step between / before the sweeps costs no extra pass:
+ *   c2b_apply_inverse  Z = K^-1 Y = L^-T D^-1 L^-1 Y   (_do_solve: solve_lower, z /= d[:, None], solve_upper); the division
+ *                      is folded into the store of the first sweep.  Z may alias Y.
+ *   c2b_dot_tril       Z = L (sqrt(d) o Y)              (_do_dot_tril: z = y * sqrt(d)[:, None], matmul_lower in place).
+ *                      Z may alias Y.
+ * d (batch,N) and W (batch,N,J) are the outputs of c2b_factor.  Scratch: the size c2b_scratch_bytes reports for
+ * C2B_OP_SOLVE_LOWER (apply_inverse) / C2B_OP_MATMUL_LOWER (dot_tril) with the same N, J, K, batch.
+ */
+int c2b_apply_inverse(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                      const double *d, const double *Y, double *Z, int32_t flags, void *scratch, size_t scratch_bytes, void *stream);
+int c2b_dot_tril(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t, const double *c, const double *U, const double *W,
+                 const double *d, const double *Y, double *Z, int32_t flags, void *scratch, size_t scratch_bytes, void *stream);
 
 /*
  * Reverse mode of the sweeps.  Replace celerite2::core::{solve_lower,solve_upper,matmul_lower,matmul_upper}_rev,

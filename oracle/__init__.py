@@ -184,3 +184,92 @@ def ref():
 
 def ref_fast():
     return _ref("libc2ref_fast.so")
+
+
+class RefPipeline:
+    """The log-likelihood (+ gradient) op chain of one series on ONE core, with every array allocated once
+    (bench.py's `--impl reference` arm and `cpu_baseline` leg: first-touch page faults of fresh outputs are not
+    charged to the reference).  `lib` is port() / ref() / ref_fast().  Not thread-safe: one instance per thread.
+
+      value(...)          assemble -> factor (in place, no workspace) -> solve_lower -> log-det, chi^2
+                          (python/celerite2/core.py:262-317,407-428; numpy.py:66-87,104-109)
+      value_and_grad(...) assemble -> factor (S) -> solve_lower (F) -> reductions -> solve_lower_rev -> factor_rev
+                          (the chain JAX runs, python/celerite2/jax/celerite2.py:34-69)
+    """
+
+    def __init__(self, lib, N, Jr, Jc, grad=True):
+        self.lib, self.N, self.Jr, self.Jc = lib, int(N), int(Jr), int(Jc)
+        J = self.J = Jr + 2 * Jc
+        z = np.zeros
+        self.c, self.a, self.U, self.V = z(J), z(N), z((N, J)), z((N, J))
+        self.d, self.W = z(N), z((N, J))
+        self.Z = z((N, 1))
+        if grad:
+            self.S, self.F = z((N, J * J)), z((N, J))
+            self.bz, self.bd = z((N, 1)), z(N)
+            self.bt, self.bc, self.bU, self.bW, self.bY = z(N), z(J), z((N, J)), z((N, J)), z((N, 1))
+            self.bt2, self.bc2, self.ba, self.bU2, self.bV = z(N), z(J), z(N), z((N, J)), z((N, J))
+
+    def _assemble(self, co, t, diag):
+        L = self.lib
+        args = [_p(_f64(v)) for v in co] + [_p(t), _p(diag), _p(self.c), _p(self.a), _p(self.U), _p(self.V)]
+        if L.kind == "port":
+            L._mats(0, self.N, self.Jr, self.Jc, *args)
+        else:
+            L._mats(self.N, self.Jr, self.Jc, *args)
+
+    def value(self, co, t, y, diag):
+        """-> (loglike, flag)"""
+        L, N, J = self.lib, self.N, self.J
+        self._assemble(co, t, diag)
+        flag = L._factor(N, J, _p(t), _p(self.c), _p(self.a), _p(self.U), _p(self.V), _p(self.a), _p(self.V), _p(None))
+        self.Z[:, 0] = y
+        L._sweep(OPS["solve_lower"], N, J, 1, _p(t), _p(self.c), _p(self.U), _p(self.V), _p(self.Z), _p(self.Z), _p(None))
+        z, d = self.Z[:, 0], self.a
+        ll = -0.5 * (np.sum(z * z / d) + np.sum(np.log(d)) + N * np.log(2 * np.pi))
+        return float(ll), int(flag)
+
+    def value_and_grad(self, co, t, y, diag):
+        """-> (loglike, bc of both reverse ops summed, flag); all per-row cotangents stay in the instance
+        (bt + bt2, bU + bU2, bV, ba, bY)."""
+        L, N, J = self.lib, self.N, self.J
+        self._assemble(co, t, diag)
+        flag = L._factor(N, J, _p(t), _p(self.c), _p(self.a), _p(self.U), _p(self.V), _p(self.d), _p(self.W), _p(self.S))
+        Y = np.ascontiguousarray(y).reshape(N, 1)
+        L._sweep(OPS["solve_lower"], N, J, 1, _p(t), _p(self.c), _p(self.U), _p(self.W), _p(Y), _p(self.Z), _p(self.F))
+        z, d = self.Z[:, 0], self.d
+        ll = -0.5 * (np.sum(z * z / d) + np.sum(np.log(d)) + N * np.log(2 * np.pi))
+        np.divide(z, d, out=self.bz[:, 0])
+        np.negative(self.bz[:, 0], out=self.bz[:, 0])
+        np.multiply(self.bz[:, 0], self.bz[:, 0], out=self.bd)
+        self.bd *= 0.5
+        self.bd -= 0.5 / d
+        L._sweep_rev(OPS["solve_lower"], N, J, 1, _p(t), _p(self.c), _p(self.U), _p(self.W), _p(Y), _p(self.Z), _p(self.F),
+                     _p(self.bz), _p(self.bt), _p(self.bc), _p(self.bU), _p(self.bW), _p(self.bY))
+        L._factor_rev(N, J, _p(t), _p(self.c), _p(self.a), _p(self.U), _p(self.V), _p(self.d), _p(self.W), _p(self.S),
+                      _p(self.bd), _p(self.bW), _p(self.bt2), _p(self.bc2), _p(self.ba), _p(self.bU2), _p(self.bV))
+        return float(ll), self.bc + self.bc2, int(flag)
+
+
+def get_celerite_matrices_rev(ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V):
+    """Adjoint of the blocked-layout assembly (c++/include/celerite2/terms.hpp:112-139; the derivative JAX takes of
+    python/celerite2/jax/terms.py:119-135), restated in numpy: cotangents of (c, a, U, V) ->
+    (b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_diag).  Checked against central differences of the forward
+    assembly in tests/test_oracle.py."""
+    ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V = map(_f64, (ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V))
+    Jr, Jc = ar.shape[0], ac.shape[0]
+    sa = np.sum(b_a)
+    b_ar = sa + np.sum(b_U[:, :Jr], axis=0)
+    b_cr = b_c[:Jr].copy()
+    arg = x[:, None] * dc[None, :]
+    co, si = np.cos(arg), np.sin(arg)
+    bU1, bU2 = b_U[:, Jr:Jr + Jc], b_U[:, Jr + Jc:]
+    bV1, bV2 = b_V[:, Jr:Jr + Jc], b_V[:, Jr + Jc:]
+    b_ac = sa + np.sum(bU1 * co + bU2 * si, axis=0)
+    b_bc = np.sum(bU1 * si - bU2 * co, axis=0)
+    b_cc = b_c[Jr:Jr + Jc] + b_c[Jr + Jc:]
+    # d/d(arg) of the four columns of one complex term
+    darg = bU1 * (-ac * si + bc * co) + bU2 * (ac * co + bc * si) - bV1 * si + bV2 * co
+    b_dc = np.sum(darg * x[:, None], axis=0)
+    b_x = darg @ dc
+    return b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_a.copy()

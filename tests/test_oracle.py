@@ -198,3 +198,72 @@ def test_sweep_rev_fd(op, name):
         return P.sweep_rev(op, *args, Z, F, cots[0])
 
     _fd_check(fwd, rev, [x.copy(), c.copy(), U.copy(), B.copy(), Y.copy()], 1)
+
+
+# ---- round 2: the restated assembly adjoint and the preallocated pipeline -------------------------------------------
+@pytest.mark.parametrize("name", ["sum3", "c2_J6", "mixed_J9"])
+def test_assembly_adjoint_restatement_against_central_differences(name):
+    """oracle.get_celerite_matrices_rev (numpy) is the derivative of the blocked assembly (terms.hpp:112-139)."""
+    import oracle
+    from helpers import ALL_KERNELS
+
+    co = [np.array(v, dtype=np.float64) for v in ALL_KERNELS[name]]
+    rng = np.random.default_rng(3)
+    N = 40
+    x = np.sort(rng.uniform(0, 10, N))
+    diag = rng.uniform(0.1, 0.3, N)
+    P = oracle.port()
+    c, a, U, V = P.get_celerite_matrices(*co, x, diag)
+    b_c, b_a, b_U, b_V = (rng.standard_normal(v.shape) for v in (c, a, U, V))
+
+    def f(co_, x_, diag_):
+        c_, a_, U_, V_ = P.get_celerite_matrices(*co_, x_, diag_)
+        return np.sum(c_ * b_c) + np.sum(a_ * b_a) + np.sum(U_ * b_U) + np.sum(V_ * b_V)
+
+    g = oracle.get_celerite_matrices_rev(*co, x, b_c, b_a, b_U, b_V)
+    eps = 1e-6
+    for i in range(6):
+        for j in range(len(co[i])):
+            cp, cm = [v.copy() for v in co], [v.copy() for v in co]
+            cp[i][j] += eps
+            cm[i][j] -= eps
+            fd = (f(cp, x, diag) - f(cm, x, diag)) / (2 * eps)
+            assert abs(fd - g[i][j]) <= 1e-7 * max(1.0, abs(fd)), (i, j)
+    for n in (0, 7, N - 1):
+        xp, xm = x.copy(), x.copy()
+        xp[n] += eps
+        xm[n] -= eps
+        fd = (f(co, xp, diag) - f(co, xm, diag)) / (2 * eps)
+        assert abs(fd - g[6][n]) <= 1e-7 * max(1.0, abs(fd))
+        dp, dm = diag.copy(), diag.copy()
+        dp[n] += eps
+        dm[n] -= eps
+        fd = (f(co, x, dp) - f(co, x, dm)) / (2 * eps)
+        assert abs(fd - g[7][n]) <= 1e-7 * max(1.0, abs(fd))
+
+
+def test_ref_pipeline_equals_op_by_op_calls():
+    """oracle.RefPipeline (preallocated buffers, raw ctypes calls) returns what the allocating wrappers return."""
+    import oracle
+    from celerite2_b200 import workloads as wl
+
+    cfg = wl.config_c2(N=3000)
+    t, y, diag = wl.light_curve(3000, 9)
+    for lib in (oracle.port(), oracle.ref(), oracle.ref_fast()):
+        if lib is None:
+            continue
+        pipe = oracle.RefPipeline(lib, 3000, 0, 3)
+        for _ in range(2):  # the second call reuses every buffer
+            ll, bc, flag = pipe.value_and_grad(cfg["coeffs"], t, y, diag)
+        c, a, U, V = lib.get_celerite_matrices(*cfg["coeffs"], t, diag)
+        flag2, d, W, S = lib.factor(t, c, a, U, V)
+        Z, F = lib.sweep("solve_lower", t, c, U, W, y[:, None])
+        z = Z[:, 0]
+        ll2 = -0.5 * (np.sum(z * z / d) + np.sum(np.log(d)) + len(t) * np.log(2 * np.pi))
+        bt, bc1, bU, bW, bY = lib.sweep_rev("solve_lower", t, c, U, W, y[:, None], Z, F, (-z / d)[:, None])
+        bt2, bc2, ba, bU2, bV = lib.factor_rev(t, c, a, U, V, d, W, S, 0.5 * z * z / d**2 - 0.5 / d, bW)
+        assert flag == flag2 == 0 and ll == ll2
+        # (the seed bd is rounded differently by the two formulations: 0.5 (z/d)^2 vs 0.5 z^2 / d^2)
+        assert np.allclose(bc, bc1 + bc2, rtol=1e-11, atol=0) and relerr(pipe.bV, bV) < 1e-12 and np.array_equal(pipe.S, S)
+        llv, _ = oracle.RefPipeline(lib, 3000, 0, 3, grad=False).value(cfg["coeffs"], t, y, diag)
+        assert abs(llv - ll) <= 1e-13 * abs(ll)

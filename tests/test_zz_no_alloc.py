@@ -45,7 +45,7 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     torch.cuda.set_device(dev)
     T = lambda x: torch.as_tensor(np.ascontiguousarray(x, dtype=np.float64), device=dev)
     stream = torch.cuda.current_stream().cuda_stream
-    lib.c2b_set_chunks_per_series(0)
+    lib.c2b_testing_set_chunks_per_series(0)
     limit = lib.c2b_noalloc_scratch_limit()
     assert limit == 8 << 20
 
@@ -85,7 +85,7 @@ def test_noalloc_rejects_oversized_problem():
     lib = _lib.lib
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
-    lib.c2b_set_chunks_per_series(0)
+    lib.c2b_testing_set_chunks_per_series(0)
     N, J, K, B = 4_000_000, 16, 1, 4
     assert lib.c2b_scratch_bytes(_lib.OP_IDS["solve_lower"], N, 0, J, K, B) > lib.c2b_noalloc_scratch_limit()
     x = torch.zeros(64, dtype=torch.float64, device=dev)  # never dereferenced: the size check comes first
