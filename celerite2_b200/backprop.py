@@ -20,7 +20,16 @@ class LinAlgError(Exception):
 def factor_fwd(t, c, a, U, V, d, W, S):
     N, J = np.shape(U)
     d_d, W_d, S_d, status = ops.factor(_up(_in(t, "t")), _up(_in(c, "c")), _up(_in(a, "a")), _up(_in(U, "U")), _up(_in(V, "V")))
-    if int(status.item()) != 0:
+    flag = int(status.item())
+    if flag != 0:
+        # backprop.cpp:48-65: the outputs are zeroed, the core writes d up to and including the failing row, W up to the row
+        # before it and S up to and including it (forward.hpp:107-128), then the exception is raised; rows computed on the
+        # device after the failure (unspecified for a chunked series) never reach the caller
+        dd, WW, SS = d_d.cpu().numpy(), W_d.cpu().numpy(), S_d.reshape(N, J, J).cpu().numpy()
+        for dst, src, rows in ((d, dd, flag + 1), (W, WW, flag), (S, SS, flag + 1)):
+            if isinstance(dst, np.ndarray) and dst.dtype == np.float64 and dst.flags.c_contiguous and dst.flags.writeable and dst.shape == src.shape:
+                dst[...] = 0.0
+                dst[:rows] = src[:rows]
         raise LinAlgError("failed to factorize or solve matrix")
     return _down(d_d, d), _down(W_d, W), _down(S_d.reshape(N, J, J), S)
 

@@ -60,6 +60,18 @@ class DeviceArray {
     out = h;
   }
 
+  // after a failed factorisation: only the first `nrows` rows are the reference's values; the rest of the caller's
+  // array stays as it was (forward.hpp:128 returns before touching later rows)
+  template <typename Derived>
+  void fetch_rows(Eigen::MatrixBase<Derived> const &out_, Eigen::Index rows, Eigen::Index cols, Eigen::Index nrows) const {
+    Eigen::MatrixBase<Derived> &out = const_cast<Eigen::MatrixBase<Derived> &>(out_);
+    RowMat h(rows, cols);
+    check(c2b_copy_to_host(h.data(), p_, n_ * sizeof(double)));
+    out.derived().resize(rows, cols);  // a no-op (contents kept) when the caller's array already has this shape
+    if (nrows > rows) nrows = rows;
+    if (nrows > 0) out.topRows(nrows) = h.topRows(nrows);
+  }
+
   private:
   size_t n_;
   double *p_;
@@ -77,21 +89,27 @@ Eigen::Index factor(const Eigen::MatrixBase<Input> &t, const Eigen::MatrixBase<C
                     Eigen::MatrixBase<LowRankOut> const &W_out, Eigen::MatrixBase<Work> const &S_out) {
   using namespace b200;
   const Eigen::Index N = U.rows(), J = U.cols();
-  // host copy of the inputs that the reference leaves in place after a failure (d aliases a, W aliases V)
-  RowMat a_h = a, V_h = V;
-  DeviceArray t_(t), c_(c), a_(a_h), U_(U), V_(V_h), d_((size_t)N), W_((size_t)(N * J));
+  DeviceArray t_(t), c_(c), a_(a), U_(U), V_(V), d_((size_t)N), W_((size_t)(N * J));
   DeviceArray S_(update_workspace ? (size_t)(N * J * J) : 1), status_(1);
-  check(c2b_copy_to_device(d_.ptr(), a_h.data(), N * sizeof(double)));
-  check(c2b_copy_to_device(W_.ptr(), V_h.data(), N * J * sizeof(double)));
   check(c2b_factor(N, (int32_t)J, 1, t_.ptr(), c_.ptr(), a_.ptr(), U_.ptr(), V_.ptr(), d_.ptr(), W_.ptr(),
                    update_workspace ? S_.ptr() : nullptr, (int64_t *)status_.ptr(), 0, nullptr, 0, nullptr));
   check(c2b_stream_synchronize(nullptr));
   int64_t flag = 0;
   check(c2b_copy_to_host(&flag, status_.ptr(), sizeof(flag)));
+  if (flag != 0) {
+    // the reference's failure semantics (forward.hpp:107-128): d is written up to and including the failing row, W up
+    // to the row before it, S up to and including it; later rows of the caller's arrays are not touched.  (A long
+    // series runs as several chunks on the device, where rows after the failure hold unspecified values: they never
+    // leave the device here.)
+    d_.fetch_rows(d_out, N, 1, (Eigen::Index)flag + 1);
+    W_.fetch_rows(W_out, N, J, (Eigen::Index)flag);
+    if (update_workspace) S_.fetch_rows(S_out, N, J * J, (Eigen::Index)flag + 1);
+    return (Eigen::Index)flag;
+  }
   d_.fetch(d_out, N, 1);
   W_.fetch(W_out, N, J);
   if (update_workspace) S_.fetch(S_out, N, J * J);
-  return (Eigen::Index)flag;
+  return 0;
 }
 
 template <typename Input, typename Coeffs, typename Diag, typename LowRank, typename DiagOut, typename LowRankOut>
