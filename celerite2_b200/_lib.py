@@ -31,6 +31,7 @@ _SIGS = {
     "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
     "c2b_add_inplace": [_i64, _vp, _vp, _vp],
+    "c2b_to_dense": [_i64, _i32] + [_vp] * 7,
     "c2b_apply_inverse": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp],
     "c2b_dot_tril": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp],
     "c2b_solve_lower_noalloc": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp],

@@ -239,9 +239,42 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
   return C2B_OK;
 }
 
+// dense N x N matrix of the semiseparable representation (forward.hpp:19-42): K(n,n) = a_n,
+// K(n,m) = K(m,n) = sum_j U(n,j) V(m,j) exp(-c_j (t_n - t_m)) for n > m.  One thread per element of the lower triangle.
+static __global__ void __launch_bounds__(256) to_dense_kernel(int64_t N, int J, const double *t, const double *c, const double *a,
+                                                              const double *U, const double *V, double *K) {
+  const int64_t total = N * N;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = i / N, m = i - n * N;
+    if (m > n) continue;
+    if (m == n) {
+      K[i] = a[n];
+      continue;
+    }
+    const double dt = t[n] - t[m];
+    double s        = 0.0;
+    for (int j = 0; j < J; ++j) s = fma(U[n * J + j] * V[m * J + j], exp(-c[j] * dt), s);
+    K[n * N + m] = s;
+    K[m * N + n] = s;
+  }
+}
+
 }  // namespace c2b
 
 extern "C" {
+
+int c2b_to_dense(int64_t N, int32_t J, const double *t, const double *c, const double *a, const double *U, const double *V, double *K_out,
+                 void *stream) {
+  c2b::OpScope _op("c2b_to_dense");
+  using namespace c2b;
+  int rc = check_common(N, J, 1);
+  if (rc) return rc;
+  C2B_REQUIRE(t && c && a && U && V && K_out, "null data pointer");
+  int64_t blocks = (N * N + 255) / 256;
+  if (blocks > 148 * 32) blocks = 148 * 32;
+  C2B_LAUNCH("to_dense_kernel", (cudaStream_t)stream, (to_dense_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(N, J, t, c, a, U, V, K_out)));
+  return C2B_OK;
+}
 
 const char *c2b_version(void) { return "celerite2_b200 0.1.0 (sm_100a)"; }
 const char *c2b_last_error(void) { return c2b::g_err; }

@@ -154,6 +154,15 @@ def get_celerite_matrices_rev(ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V, b_x
     return b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_diag
 
 
+def to_dense(t, c, a, U, V):
+    """-> K (N,N): the dense matrix of the representation (forward.hpp:19-42; test utility)"""
+    t, c, a, U, V = [_f64(v, n) for v, n in zip((t, c, a, U, V), "tcaUV")]
+    N, J = U.shape
+    K = torch.empty((N, N), dtype=torch.float64, device=U.device)
+    check(lib.c2b_to_dense(N, J, _ptr(t), _ptr(c), _ptr(a), _ptr(U), _ptr(V), _ptr(K), _stream()))
+    return K
+
+
 # ---- factor --------------------------------------------------------------------------------------------------
 def factor(t, c, a, U, V, d=None, W=None, workspace=True, status=None):
     """-> (d, W, S, status).  d / W default to fresh tensors; pass d=a, W=V for the in-place form.

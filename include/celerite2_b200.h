@@ -78,6 +78,14 @@ const char *c2b_profile_report(void);
 void c2b_testing_set_chunks_per_series(int64_t chunks);
 
 /*
+ * Dense N x N matrix of the semiseparable representation: replaces celerite2::core::to_dense,
+ * c++/include/celerite2/forward.hpp:19-42 (a test utility there as here: O(N^2 J) work, N^2 doubles of output).
+ * t (N)  c (J)  a (N)  U,V (N,J)  ->  K_out (N,N) row-major, symmetric.
+ */
+int c2b_to_dense(int64_t N, int32_t J, const double *t, const double *c, const double *a, const double *U, const double *V, double *K_out,
+                 void *stream);
+
+/*
  * a/U/V (and c) assembly from the kernel coefficients.
  *   layout 0 "blocked"     [real.. | cos.. | sin..]       replaces celerite2::Term::get_celerite_matrices,
  *                                                         c++/include/celerite2/terms.hpp:112-139

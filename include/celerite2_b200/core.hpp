@@ -10,6 +10,9 @@
 //   forward.hpp:285-392                        general_matmul_*  -> c2b_general_matmul_lower / _upper
 //   interface.hpp:37-220                       the no-workspace overloads
 //   reverse.hpp:10-217                         *_rev             -> c2b_*_rev
+//   forward.hpp:19-42                          to_dense          -> c2b_to_dense
+// The headers under include/celerite2/ (celerite2.h, core.hpp, forward.hpp, interface.hpp, reverse.hpp, terms.hpp) carry
+// the reference's file names, so `#include <celerite2/celerite2.h>` with -I<this repo>/include is the whole switch.
 //
 // Operands may be arbitrary Eigen expressions (they are evaluated into contiguous row-major host buffers first,
 // which also makes the reference's aliasing contracts hold trivially); outputs are resized like the reference's
@@ -80,6 +83,18 @@ class DeviceArray {
 }  // namespace b200
 
 namespace core {
+
+// ---- to_dense (forward.hpp:19-42) ----------------------------------------------------------------------------------
+template <typename Input, typename Coeffs, typename Diag, typename LowRank, typename Dense>
+void to_dense(const Eigen::MatrixBase<Input> &t, const Eigen::MatrixBase<Coeffs> &c, const Eigen::MatrixBase<Diag> &a,
+              const Eigen::MatrixBase<LowRank> &U, const Eigen::MatrixBase<LowRank> &V, Eigen::MatrixBase<Dense> const &K_out) {
+  using namespace b200;
+  const Eigen::Index N = U.rows(), J = U.cols();
+  DeviceArray t_(t), c_(c), a_(a), U_(U), V_(V), K_((size_t)(N * N));
+  check(c2b_to_dense(N, (int32_t)J, t_.ptr(), c_.ptr(), a_.ptr(), U_.ptr(), V_.ptr(), K_.ptr(), nullptr));
+  check(c2b_stream_synchronize(nullptr));
+  K_.fetch(K_out, N, N);
+}
 
 // ---- factor --------------------------------------------------------------------------------------------------
 template <bool update_workspace = true, typename Input, typename Coeffs, typename Diag, typename LowRank, typename DiagOut,

@@ -9,6 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 OUT = os.path.join(HERE, "_bin", "test_dropin")
+PROGRAMS = ("test_dropin", "test_names")  # test_names includes <celerite2/celerite2.h>: the shim headers under the reference's names
 
 
 def eigen_include():
@@ -18,21 +19,27 @@ def eigen_include():
     return None
 
 
-def build(force=False):
+def build(force=False, name="test_dropin"):
+    out = os.path.join(HERE, "_bin", name)
     inc = eigen_include()
     if inc is None:
-        return OUT if os.path.exists(OUT) else None
-    src = os.path.join(HERE, "test_dropin.cpp")
-    deps = [src, os.path.join(ROOT, "include", "celerite2_b200", "core.hpp"), os.path.join(ROOT, "include", "celerite2_b200.h")]
-    if not force and os.path.exists(OUT) and all(os.path.getmtime(d) <= os.path.getmtime(OUT) for d in deps):
-        return OUT
-    os.makedirs(os.path.dirname(OUT), exist_ok=True)
+        return out if os.path.exists(out) else None
+    src = os.path.join(HERE, name + ".cpp")
+    deps = [src, os.path.join(ROOT, "include", "celerite2_b200", "core.hpp"), os.path.join(ROOT, "include", "celerite2_b200.h"),
+            os.path.join(ROOT, "include", "celerite2", "terms.hpp")]
+    if not force and os.path.exists(out) and all(os.path.getmtime(d) <= os.path.getmtime(out) for d in deps):
+        return out
+    os.makedirs(os.path.dirname(out), exist_ok=True)
     cmd = ["g++", "-std=c++17", "-O1", "-I", os.path.join(ROOT, "include"), "-I", inc, src, "-L", os.path.join(ROOT, "celerite2_b200"),
-           "-lcelerite2_b200", "-Wl,-rpath,$ORIGIN/../../../celerite2_b200", "-o", OUT]
+           "-lcelerite2_b200", "-Wl,-rpath,$ORIGIN/../../../celerite2_b200", "-o", out]
     print("[cpp] " + " ".join(cmd), flush=True)
     subprocess.check_call(cmd)
-    return OUT
+    return out
+
+
+def build_all(force=False):
+    return [build(force, name) for name in PROGRAMS]
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv))
+    print(build_all(force="--force" in sys.argv))
