@@ -106,7 +106,7 @@ def load_peaks():
 # =====================================================================================================================
 # host-side inputs of each workload (numpy; identical for both arms)
 # =====================================================================================================================
-def host_inputs(name, rank, world, small=False):
+def host_inputs(name, rank, world, small=False, batch_per_gpu=None):
     """-> dict(cfg, coeffs (6 arrays), t, y, diag [, Y]); batched arrays carry the leading batch axis of THIS rank's shard."""
     if name == "c1":
         cfg = wl.config_c1()
@@ -117,7 +117,7 @@ def host_inputs(name, rank, world, small=False):
         t, y, diag = wl.light_curve(cfg["N"], cfg["seed"])  # one series for the whole job (split across ranks when world > 1)
         return dict(cfg=cfg, coeffs=cfg["coeffs"], t=t, y=y, diag=diag)
     if name == "c3":
-        B = 256 if small else SERIES_PER_GPU_C3
+        B = batch_per_gpu or (256 if small else SERIES_PER_GPU_C3)
         full = wl.config_c3(batch=B * world)
         lo = rank * B
         co = tuple(np.ascontiguousarray(v[lo:lo + B]) for v in full["coeffs"])
@@ -129,7 +129,7 @@ def host_inputs(name, rank, world, small=False):
         cfg = dict(full, batch=B, N=N)
         return dict(cfg=cfg, coeffs=co, t=t, y=y, diag=yerr**2)
     if name == "c5":
-        B = 64 if small else SAMPLES_PER_GPU_C5
+        B = batch_per_gpu or (64 if small else SAMPLES_PER_GPU_C5)
         full = wl.config_c5(batch=B * world)
         lo = rank * B
         co = tuple(np.ascontiguousarray(v[lo:lo + B]) for v in full["coeffs"])
@@ -290,7 +290,7 @@ def run_reference_arm(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
         return
-    inp = host_inputs(args.workload, 0, world, small=args.small)
+    inp = host_inputs(args.workload, 0, world, small=args.small, batch_per_gpu=args.batch_per_gpu)
     run = ReferenceRunner(args.workload, inp)
     for _ in range(max(1, min(args.warmup, 3))):
         run.step()
@@ -826,7 +826,7 @@ def run_c4(ctx, inp):
 def run_ours(args):
     ctx = Ctx(args)
     name = args.workload
-    inp = host_inputs(name, ctx.rank, ctx.world, small=args.small)
+    inp = host_inputs(name, ctx.rank, ctx.world, small=args.small, batch_per_gpu=args.batch_per_gpu)
     if name == "c2" and ctx.world > 1:
         line = run_split_series(ctx, inp)
     elif name == "c4":
@@ -852,6 +852,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(META))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch-per-gpu", type=int, default=None, help="c3 / c5: series (samples) per GPU instead of the 1/8 share")
     ap.add_argument("--small", action="store_true", help="reduced sizes (development only; never a bench line)")
     args = ap.parse_args()
     if args.impl == "reference":

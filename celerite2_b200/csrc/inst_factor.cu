@@ -32,7 +32,7 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
     }
     if (phase == 2) {
       if ((rc = seg_import_state<Lft<JT>>(g.J, 1, g.C, sb.states, g.seg.state_in, stream))) return rc;
-      if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, g.seg.state_in, stream, 2))) return rc;
       g.carry = sb.states;
     } else if (g.C > 1) {
       if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
@@ -88,7 +88,7 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
     }
     if (phase == 2) {
       if ((rc = seg_import_state<Cong<JT>>(g.J, 1, g.C, sb.states, g.seg.state_in, stream))) return rc;
-      if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, g.seg.state_in, stream, 2))) return rc;
       g.carry = sb.states;
     } else if (g.C > 1) {
       if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;

@@ -47,7 +47,7 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
     }
     if (phase == 2) {
       if ((rc = seg_import_state<AffV<JT>>(a.J, 1, a.C, sb.states, a.seg.state_in, stream))) return rc;
-      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, a.seg.state_in, stream, 2))) return rc;
       a.carry = sb.states;
     } else if (a.C > 1) {
       if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream))) return rc;
@@ -95,7 +95,7 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     }
     if (phase == 2) {
       if ((rc = seg_import_state<AffV<JT>>(a.J, 1, a.C, sb.states, a.seg.state_in, stream))) return rc;
-      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 2))) return rc;
+      if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, a.seg.state_in, stream, 2))) return rc;
       a.carry = sb.states;
     } else if (a.C > 1) {
       if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream))) return rc;

@@ -239,6 +239,128 @@ C2B_DEV void slice_out(double *dst, const double *src, int n, int loc, int glob,
   }
 }
 
+
+// ---- prefix blocks (round 2) ---------------------------------------------------------------------------------------
+// The tree above spends one combine latency per level on the way up AND one apply latency per level on the way down
+// (26 dependent rounds for 7,000 chunks; r01i profile: the scans are 27 % of the c2 step at ~0 bytes moved -- pure
+// depth x latency).  Here a CTA owns a block of BS = 2 nwarps consecutive elements of one "level group" and turns them
+// into their INCLUSIVE PREFIXES P_i = e_0 o ... o e_i inside shared memory with the divide-and-conquer (Sklansky)
+// network: log2(BS) rounds, BS / 2 independent warp-cooperative combines per round, one per warp.  The block's last
+// prefix is the block aggregate and becomes one element of the next level group.  On the way down a block receives
+// the state s entering it and produces the states entering its elements in ONE round of independent applies:
+// state_0 = s, state_i = apply(P_{i-1}, s).  Depth for C = 7,104: 5 + 5 + 3 combine rounds up, 1 + 2 + 2 apply rounds
+// down (BS = 32) instead of 13 + 13.
+//
+// Level groups: group 0 = the C leaves, group g + 1 = the ceil(cnt_g / BS) block aggregates of group g; the top group
+// has at most BS elements.  nodes[off_g + i] holds element i of group g, overwritten in place by its prefix within its
+// block; states[off_g + i] the state entering it.
+struct PLevels {
+  int ng;            // number of level groups; cnt[ng-1] <= BS
+  int64_t cnt[12];   // elements per group
+  int64_t off[12];   // offset of each group inside one series (in elements)
+};
+
+static inline PLevels make_plevels(int64_t leaves, int BS) {
+  PLevels pl;
+  memset(&pl, 0, sizeof(pl));
+  int g       = 0;
+  int64_t cnt = leaves, off = 0;
+  for (;;) {
+    pl.cnt[g] = cnt;
+    pl.off[g] = off;
+    off += cnt;
+    ++g;
+    if (cnt <= BS) break;
+    cnt = (cnt + BS - 1) / BS;
+  }
+  pl.ng = g;
+  return pl;
+}
+
+// where element i of a block lives after the rounds of the network: it moved to the other buffer every time it was
+// updated, i.e. once per set bit of its index within the block
+C2B_DEV int pbuf_of(int i) { return __popc((unsigned)i) & 1; }
+
+// one CTA per (series, block of BS elements of group g) and column slice (blockIdx.y).
+//   do_up   : scan the block (elements -> prefixes, written back in place); not the top group: aggregate -> group g + 1
+//   do_down : states of the block's elements from the state entering the block: the top group is seeded from `init`
+//             (NULL = zero state), the others read states[off_{g+1} + blk]
+template <class Mon>
+__global__ void __launch_bounds__(kCoopThreadsMax) pscan_block(int J_, int K, int kb, PLevels pl, int g, int BS, int64_t stride,
+                                                              bool do_up, bool do_down, double *nodes_all, double *states_all,
+                                                              const double *init) {
+  const int J = Mon::kJT ? Mon::kJT : J_;
+  extern __shared__ __align__(16) double sm_all[];
+  const int k0  = blockIdx.y * kb;
+  const int kl  = K - k0 < kb ? K - k0 : kb;
+  const int esg = Mon::esize(J, K), ssg = Mon::ssize(J, K);
+  const int es = Mon::esize(J, kl), ss = Mon::ssize(J, kl);
+  const int eh = Mon::ehead(J), sh = Mon::shead(J);
+  const int ego = eh + Mon::ecol(J) * k0, sgo = sh + Mon::scol(J) * k0;
+  const int wsm    = Coop<Mon>::wsmem(J, kl);
+  const int nwarps = blockDim.x >> 5, wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool top     = g == pl.ng - 1;
+  const int64_t nblk = (pl.cnt[g] + BS - 1) / BS;
+  const int64_t b = blockIdx.x / nblk, blk = blockIdx.x % nblk;
+  const int64_t rem = pl.cnt[g] - blk * BS;
+  const int cnt     = rem < BS ? (int)rem : BS;
+  double *const buf0 = sm_all, *const buf1 = buf0 + (size_t)BS * es;
+  auto bsel          = [&](int p) { return p ? buf1 : buf0; };
+  double *sin_ = buf1 + (size_t)BS * es;            // ss: the state entering the block
+  double *sout = sin_ + ss;                         // BS * ss
+  double *sm   = sout + (size_t)BS * ss + (size_t)wib * wsm;
+  double *elems = nodes_all + (b * stride + pl.off[g] + blk * BS) * esg;
+  slice_in(buf0, elems, cnt, es, esg, eh, ego);
+  __syncthreads();
+  if (do_up) {
+    for (int s = 0; (1 << s) < cnt; ++s) {
+      // the BS / 2 elements with bit s set combine with the last element of the lower half of their 2^(s+1) group
+      for (int r = wib; r < BS / 2; r += nwarps) {
+        const int i = ((r >> s) << (s + 1)) | (1 << s) | (r & ((1 << s) - 1));
+        if (i < cnt) {
+          const int j  = ((i >> s) << s) - 1;
+          const int lo = i & ((1 << s) - 1);  // bits of i below s: the updates i has seen so far
+          const double *ej = bsel(pbuf_of(j & ((1 << s) - 1))) + (size_t)j * es;
+          const double *ei = bsel(pbuf_of(lo)) + (size_t)i * es;
+          double *eo       = bsel(pbuf_of(lo) ^ 1) + (size_t)i * es;
+          Coop<Mon>::wcombine(lane, J, kl, ej, ei, eo, sm);
+        }
+      }
+      __syncthreads();
+    }
+    // prefixes back in place (element i sits in buffer popc(i) & 1)
+    for (int e = threadIdx.x; e < cnt * es; e += blockDim.x) {
+      const int i = e / es, r = e - i * es;
+      if (r >= eh || blockIdx.y == 0) elems[(size_t)i * esg + (r < eh ? r : r - eh + ego)] = bsel(pbuf_of(i))[e];
+    }
+    if (!top) {
+      double *agg       = nodes_all + (b * stride + pl.off[g + 1] + blk) * esg;
+      const double *src = bsel(pbuf_of(cnt - 1)) + (size_t)(cnt - 1) * es;
+      for (int r = threadIdx.x; r < es; r += blockDim.x)
+        if (r >= eh || blockIdx.y == 0) agg[r < eh ? r : r - eh + ego] = src[r];
+    }
+  }
+  if (do_down) {
+    double *states = states_all + b * stride * ssg;
+    if (top) {
+      for (int e = threadIdx.x; e < ss; e += blockDim.x) sin_[e] = init ? init[b * ssg + (e < sh ? e : e - sh + sgo)] : 0.0;
+    } else {
+      slice_in(sin_, states + (pl.off[g + 1] + blk) * ssg, 1, ss, ssg, sh, sgo);
+    }
+    __syncthreads();
+    for (int i = wib; i < cnt; i += nwarps) {
+      if (i == 0) {
+        wcopy(lane, ss, sin_, sout);
+      } else {
+        const double *e = (do_up ? bsel(pbuf_of(i - 1)) : buf0) + (size_t)(i - 1) * es;
+        Coop<Mon>::wapply(lane, J, kl, e, sin_, sout + (size_t)i * ss, sm);
+      }
+    }
+    __syncthreads();
+    slice_out(states + (pl.off[g] + blk * BS) * ssg, sout, cnt, ss, ssg, sh, sgo, true);
+  }
+}
+
 // DIR: 0 = up only, 1 = down only, 2 = up then down (the launch that contains the top of the tree)
 template <class Mon, int DIR>
 __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int kb, int64_t batch, Levels lv, int lb, int nlev,
@@ -286,6 +408,96 @@ __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int
   }
 }
 
+
+// Developer switch (environment, read once): C2B_SCAN_TREE=1 keeps the round-1 block-resident trees for A/B runs.
+static inline bool scan_use_tree() {
+  static const bool v = getenv("C2B_SCAN_TREE") != nullptr;
+  return v;
+}
+
+// Block size / warps / columns per slice of the prefix-block scan: the largest block whose shared memory (two element
+// buffers, the states, the warps' scratch) lets two CTAs share an SM, else one CTA per SM, narrower slices last.
+template <class Mon>
+struct PScanPlan {
+  int BS, nwarps, kb;
+  size_t smem;
+  bool ok;
+};
+template <class Mon>
+static inline size_t pscan_smem(int J, int kb, int BS, int nwarps) {
+  return ((size_t)2 * BS * Mon::esize(J, kb) + (size_t)(BS + 1) * Mon::ssize(J, kb) + (size_t)nwarps * Coop<Mon>::wsmem(J, kb)) * sizeof(double);
+}
+template <class Mon>
+static inline PScanPlan<Mon> pscan_plan(int J, int K) {
+  static const int cand[] = {32, 16, 8, 4, 2};
+  PScanPlan<Mon> pp{2, 1, K, 0, false};
+  const int ec = Mon::ecol(J) + Mon::scol(J);
+  for (int pass = 0; pass < 2 && !pp.ok; ++pass) {
+    const size_t budget = pass == 0 ? 110 * 1024 : 200 * 1024;
+    for (int BS : cand) {
+      if (pass == 0 && BS < 16) break;
+      const int nwarps = BS / 2;
+      int kb           = K;
+      if (ec > 0) {
+        while (kb > 1 && pscan_smem<Mon>(J, kb, BS, nwarps) > budget) kb = (kb + 1) / 2;
+        if (kb < (K < 4 ? K : 4) && BS > 2) continue;  // slices that narrow: prefer a smaller block
+        const int nsl = (K + kb - 1) / kb;
+        kb            = (K + nsl - 1) / nsl;  // balanced slices
+      }
+      const size_t smem = pscan_smem<Mon>(J, kb, BS, nwarps);
+      if (smem <= budget) {
+        pp = PScanPlan<Mon>{BS, nwarps, kb, smem, true};
+        break;
+      }
+    }
+  }
+  return pp;
+}
+
+// mode 0: everything.  mode 1: up only (the aggregate of the whole series is the last prefix of the top group).
+// mode 2: down only, the state entering the series comes from `init` (NULL = zero).
+template <class Mon>
+static inline int run_pscan(int J, int K, int64_t batch, int64_t leaves, double *nodes, double *states, const double *init,
+                            cudaStream_t stream, int mode) {
+  const PScanPlan<Mon> pp = pscan_plan<Mon>(J, K);
+  if (!pp.ok) {
+    set_error("scan: summary element too large for a shared-memory block (J = %d, K = %d)", J, K);
+    return C2B_ERR_INVALID_ARGUMENT;
+  }
+  const Levels lv  = make_levels(leaves);  // lv.total is the per-series stride of the scratch arrays (host_common.cuh: take_scan)
+  const PLevels pl = make_plevels(leaves, pp.BS);
+  static std::atomic<bool> attr_done[64];  // per instantiation and device; a race only repeats the (idempotent) call
+  int dev = 0;
+  C2B_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_done[dev].load(std::memory_order_acquire)) {
+    C2B_CUDA(cudaFuncSetAttribute(pscan_block<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    if (dev >= 0 && dev < 64) attr_done[dev].store(true, std::memory_order_release);
+  }
+  const unsigned nslices = (unsigned)((K + pp.kb - 1) / pp.kb);
+  const int top          = pl.ng - 1;
+  auto launch = [&](const char *name, int g, bool up, bool down) -> int {
+    const dim3 grid((unsigned)(batch * ((pl.cnt[g] + pp.BS - 1) / pp.BS)), nslices);
+    C2B_LAUNCH(name, stream,
+               (pscan_block<Mon><<<grid, pp.nwarps * 32, pp.smem, stream>>>(J, K, pp.kb, pl, g, pp.BS, lv.total, up, down, nodes, states, init)));
+    return C2B_OK;
+  };
+  int rc;
+  if (mode != 2)
+    for (int g = 0; g < top; ++g)
+      if ((rc = launch("scan_up_block", g, true, false))) return rc;
+  if (mode == 0) {
+    if ((rc = launch("scan_top_block", top, true, true))) return rc;
+  } else if (mode == 1) {
+    if (pl.cnt[top] > 1 && (rc = launch("scan_up_block", top, true, false))) return rc;
+  } else {
+    if ((rc = launch("scan_down_block", top, false, true))) return rc;
+  }
+  if (mode != 1)
+    for (int g = top - 1; g >= 0; --g)
+      if ((rc = launch("scan_down_block", g, false, true))) return rc;
+  return C2B_OK;
+}
+
 // Scratch needed by a scan over `leaves` chunks per series.
 template <class Mon>
 static inline void scan_sizes(int J, int K, int64_t batch, int64_t leaves, size_t *node_doubles, size_t *state_doubles) {
@@ -303,6 +515,7 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop) {
+    if (!scan_use_tree()) return run_pscan<Mon>(J, K, batch, leaves, nodes, states, init, stream, mode);
     // levels per launch / warps per CTA / columns per slice: the largest configuration whose shared memory (sized
     // for the launch that holds nodes and states) lets two CTAs share an SM
     static const int cand[][2] = {{5, 16}, {5, 8}, {4, 8}, {4, 4}, {3, 4}, {2, 2}, {1, 1}};
@@ -401,11 +614,21 @@ template <class Mon>
 static inline int seg_export_root(int J, int K, int64_t leaves, const double *nodes, double *summary_out, cudaStream_t stream) {
   const Levels lv = make_levels(leaves);
   const int es    = Mon::esize(J, K);
-  C2B_CUDA(cudaMemcpyAsync(summary_out, nodes + lv.off[lv.nlev - 1] * es, sizeof(double) * es, cudaMemcpyDeviceToDevice, stream));
+  int64_t root    = lv.off[lv.nlev - 1];
+  if constexpr (Mon::kCoop) {
+    if (!scan_use_tree()) {  // prefix blocks: the aggregate of the series is the last prefix of the top group
+      const PLevels pl = make_plevels(leaves, pscan_plan<Mon>(J, K).BS);
+      root             = pl.off[pl.ng - 1] + pl.cnt[pl.ng - 1] - 1;
+    }
+  }
+  C2B_CUDA(cudaMemcpyAsync(summary_out, nodes + root * es, sizeof(double) * es, cudaMemcpyDeviceToDevice, stream));
   return C2B_OK;
 }
 template <class Mon>
 static inline int seg_import_state(int J, int K, int64_t leaves, double *states, const double *state_in, cudaStream_t stream) {
+  if constexpr (Mon::kCoop) {
+    if (!scan_use_tree()) return C2B_OK;  // prefix blocks take the entering state through run_scan's `init`
+  }
   const Levels lv = make_levels(leaves);
   const int ss    = Mon::ssize(J, K);
   double *dst     = states + lv.off[lv.nlev - 1] * ss;

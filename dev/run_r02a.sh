@@ -7,4 +7,5 @@ timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -q >> gpurun_out/r
 for w in c2 c1 c4 c5 c3; do
   C2B_BENCH_NO_ASSERT=1 timeout 600 python bench.py --workload $w --steps 10 --warmup 3 > gpurun_out/r02a_bench_$w.json 2> gpurun_out/r02a_bench_$w.err; echo "bench $w rc=$?" >> gpurun_out/r02a_pytest.log
 done
-tail -5 gpurun_out/r02a_pytest.log
+C2B_SCAN_TREE=1 C2B_BENCH_NO_ASSERT=1 timeout 600 python bench.py --workload c2 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r02a_bench_c2_tree.json 2> gpurun_out/r02a_bench_c2_tree.err
+tail -8 gpurun_out/r02a_pytest.log
