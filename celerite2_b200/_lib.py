@@ -17,7 +17,7 @@ _sz = ctypes.c_size_t
 OP_IDS = {
     "factor": 0, "factor_rev": 1, "solve_lower": 2, "solve_upper": 3, "matmul_lower": 4, "matmul_upper": 5,
     "solve_lower_rev": 6, "solve_upper_rev": 7, "matmul_lower_rev": 8, "matmul_upper_rev": 9,
-    "general_matmul": 10, "assemble_rev": 11,
+    "general_matmul": 10, "assemble_rev": 11, "predict_variance": 12,
 }
 SHARED_T, SHARED_C, SHARED_Y, ACCUMULATE = 1, 2, 4, 8
 
@@ -31,6 +31,8 @@ _SIGS = {
     "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
     "c2b_add_inplace": [_i64, _vp, _vp, _vp],
+    "c2b_kernel_matrix": [_i64, _i64, _i32, _i32] + [_vp] * 10,
+    "c2b_predict_variance": [_i64, _i64, _i32, _i32] + [_vp] * 10 + [_vp, _sz, _vp],
     "c2b_to_dense": [_i64, _i32] + [_vp] * 7,
     "c2b_apply_inverse": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp],
     "c2b_dot_tril": [_i64, _i32, _i32, _i64] + [_vp] * 7 + [_i32, _vp, _sz, _vp],

@@ -339,6 +339,7 @@ size_t c2b_scratch_bytes(int32_t op, int64_t N, int64_t M, int32_t J, int32_t K,
     case C2B_OP_MATMUL_UPPER_REV: return scratch_sweep_rev(false, N, J, K, batch);
     case C2B_OP_GENERAL_MATMUL: return scratch_general_matmul(M > 0 ? M : N, J, K);
     case C2B_OP_ASSEMBLE_REV: return scratch_assemble_rev(N, J, J, batch);  // upper bound: Jr, Jc <= J
+    case C2B_OP_PREDICT_VARIANCE: return scratch_predict_variance(N, M > 0 ? M : N);
     default: return 0;
   }
 }

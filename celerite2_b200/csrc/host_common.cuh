@@ -81,5 +81,6 @@ size_t scratch_factor_rev(int64_t N, int J, int64_t batch);
 size_t scratch_general_matmul(int64_t M, int J, int K);
 size_t scratch_assemble_rev(int64_t N, int Jr, int Jc, int64_t batch);
 size_t scratch_norm_logdet(int64_t N, int64_t batch);
+size_t scratch_predict_variance(int64_t N, int64_t M);
 
 }  // namespace c2b

@@ -56,7 +56,8 @@ enum c2b_op {
   C2B_OP_MATMUL_LOWER_REV = 8,
   C2B_OP_MATMUL_UPPER_REV = 9,
   C2B_OP_GENERAL_MATMUL   = 10,
-  C2B_OP_ASSEMBLE_REV     = 11
+  C2B_OP_ASSEMBLE_REV     = 11,
+  C2B_OP_PREDICT_VARIANCE = 12
 };
 
 const char *c2b_version(void);
@@ -84,6 +85,23 @@ void c2b_testing_set_chunks_per_series(int64_t chunks);
  */
 int c2b_to_dense(int64_t N, int32_t J, const double *t, const double *c, const double *a, const double *U, const double *V, double *K_out,
                  void *stream);
+
+/*
+ * Dense pieces of the predictive distribution, python/celerite2/core.py:52-66,134-150.  The reference
+ * builds K* = kernel.get_value(x[:, None] - xs[None, :]) (N x M) in numpy, applies K^-1 to it and takes
+ * k(0) - einsum("ij,ij->j", K*, K^-1 K*) (numpy.py:24-25).
+ *   c2b_kernel_matrix      K_out (N,M) row-major = k(x1[n] - x2[m]) from the six coefficient vectors (terms.py:64-85):
+ *                          K* with x1 = x, x2 = xs; the prior covariance of the predictions with x1 = x2 = xs.
+ *   c2b_predict_variance   var_out (M) = k(0) - sum_n k(x1[n] - x2[m]) Z[n][m] with Z (N,M) = K^-1 K* (c2b_apply_inverse on
+ *                          the output of c2b_kernel_matrix); K* is not read back, its entries are re-evaluated in the
+ *                          reduction.  Scratch: c2b_scratch_bytes(C2B_OP_PREDICT_VARIANCE, N, M, ...).
+ * Coefficients in device memory: ar, cr (Jr)  ac, bc, cc, dc (Jc).
+ */
+int c2b_kernel_matrix(int64_t N, int64_t M, int32_t Jr, int32_t Jc, const double *ar, const double *cr, const double *ac, const double *bc,
+                      const double *cc, const double *dc, const double *x1, const double *x2, double *K_out, void *stream);
+int c2b_predict_variance(int64_t N, int64_t M, int32_t Jr, int32_t Jc, const double *ar, const double *cr, const double *ac,
+                         const double *bc, const double *cc, const double *dc, const double *x1, const double *x2, const double *Z,
+                         double *var_out, void *scratch, size_t scratch_bytes, void *stream);
 
 /*
  * a/U/V (and c) assembly from the kernel coefficients.
