@@ -650,6 +650,7 @@ def run_split_series(ctx, inp):
     t_d, y_d, d_d = t_h.to(ctx.dev), y_h.to(ctx.dev), d_h.to(ctx.dev)
     J = co_d[0].shape[-1] + 2 * co_d[2].shape[-1]
     ev = segments.SplitSeries(co_d, t_d, y_d, d_d, r0, r1)
+    graphed = (not os.environ.get("C2B_SPLIT_EAGER")) and ev.capture()
     out_h = torch.empty(ev.packed.numel(), dtype=torch.float64).pin_memory()
 
     def step_resident():
@@ -673,7 +674,7 @@ def run_split_series(ctx, inp):
         raise SystemExit("factorisation failed")
     sampler = ClockSampler(ctx.local) if rank == 0 else None
     ms_step, wall_step = ctx.timed(step_resident, args.steps)
-    per_op, per_kernel, launches, ms_prof = ctx.profile(step_resident, args.steps)
+    per_op, per_kernel, launches, ms_prof = ctx.profile(ev._step_eager, args.steps)  # eager: the events sit between launches
     for _ in range(2):
         step_e2e()
     ms_e2e, wall_e2e = ctx.timed(step_e2e, args.steps)
@@ -726,7 +727,8 @@ def run_split_series(ctx, inp):
             "multi_gpu": "one series, contiguous row ranges per rank; per operator: summarise -> NCCL all-gather of one summary "
                          "per rank (<= %d bytes) -> device-side carry fold -> apply; one all-reduce of the log-likelihood and "
                          "coefficient gradients at the end" % (3 * J * J * 8),
-            "launch": "kernels launched from Python (the exchange sits between them)"}),
+            "launch": ("one CUDA graph per evaluation: kernels and NCCL exchanges replayed together" if graphed else
+                       "kernels and NCCL exchanges launched from Python (graph capture unavailable: %s)" % getattr(ev, "capture_error", "disabled"))}),
         "clocks": clocks,
         "e2e": {"value": N / (ms_e2e * 1e-3), "unit": "points/s", "h2d_bytes_per_step": 8 * (t_h.numel() + y_h.numel() + d_h.numel() + sum(v.numel() for v in co_h)),
                 "d2h_bytes_per_step": 8 * ev.packed.numel(), "ms_per_step": ms_e2e, "wall_ms_per_step": wall_e2e,

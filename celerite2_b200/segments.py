@@ -285,13 +285,36 @@ class SplitSeries:
         ncoef = sum(v.numel() for v in self.coeffs)
         self.n_out = 2 + ncoef + 1
         self.packed = torch.zeros(2 + ncoef + self.world + 1, dtype=torch.float64, device=dev)
-        self._first = True
+        self._graph, self._result = None, None
+
+    def capture(self, warmup=3):
+        """Record one evaluation -- kernels AND the NCCL exchanges between them -- in a CUDA graph (every rank of the group
+        must call this together); `step()` then replays it: the host no longer sits between summarise, exchange, carry and
+        apply of the four operators.  Returns False (and stays eager) if the capture fails."""
+        for _ in range(warmup):
+            self._step_eager()
+        torch.cuda.synchronize()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                res = self._step_eager()
+            torch.cuda.synchronize()
+        except Exception as e:  # pragma: no cover  (depends on the NCCL / driver combination)
+            self._graph, self.capture_error = None, repr(e)
+            torch.cuda.synchronize()
+            return False
+        self._graph, self._result = g, res
+        return True
 
     def step(self):
+        if self._graph is not None:
+            self._graph.replay()
+            return self._result
+        return self._step_eager()
+
+    def _step_eager(self):
         seg, dist = self.seg, self.dist
-        if not self._first:
-            seg.reassemble()
-        self._first = False
+        seg.reassemble()
         red = None
         for op, summarise, apply in _STEPS:
             mine = getattr(seg, summarise)()
