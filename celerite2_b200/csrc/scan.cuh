@@ -409,9 +409,15 @@ __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int
 }
 
 
-// Developer switch (environment, read once): C2B_SCAN_TREE=1 keeps the round-1 block-resident trees for A/B runs.
+// Developer switch (environment, read once): C2B_SCAN=tree selects the round-1 block-resident trees, C2B_SCAN=prefix the
+// prefix blocks (A/B runs on the GPU box).  kScanDefaultTree is the default when the variable is unset.
+constexpr bool kScanDefaultTree = true;
 static inline bool scan_use_tree() {
-  static const bool v = getenv("C2B_SCAN_TREE") != nullptr;
+  static const bool v = [] {
+    const char *e = getenv("C2B_SCAN");
+    if (!e) return kScanDefaultTree;
+    return e[0] == 't' || e[0] == 'T';
+  }();
   return v;
 }
 
