@@ -17,7 +17,9 @@ struct FactorTile {
 };
 
 // tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
-template <int J>
+// DIRECT: lane c writes its column of a workspace row (J contiguous doubles at offset J*c of the row) straight from
+// registers with 16-byte stores instead of collecting SR rows in shared memory first (A/B switch C2B_S_DIRECT).
+template <int J, bool DIRECT = false>
 __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;  // groups per CTA
@@ -32,7 +34,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
   __shared__ __align__(16) double sprop[GP * R * JE];
   __shared__ __align__(16) double sxch[GP * 2 * JE];
   __shared__ double scc[GP * JE];
-  __shared__ __align__(16) double srows[GP * SS];  // the tile's S rows, flushed with wide stores once per tile
+  __shared__ __align__(16) double srows[DIRECT ? 2 : GP * SS];  // the tile's S rows, flushed with wide stores once per tile
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
   const int64_t unit   = (int64_t)blockIdx.x * GP + gin;
@@ -47,7 +49,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
   const double *a = g.a + b * g.N, *U = g.U + b * NJ, *V = g.V + b * NJ;
   double *d = g.d + b * g.N, *W = g.W + b * NJ;
   double *S = g.S ? g.S + b * NJ * J : nullptr;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 2 * JE, *sbuf = srows + gin * SS;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 2 * JE, *sbuf = srows + (DIRECT ? 0 : gin * SS);
   const GCopy<G> cp{c};
   const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
@@ -108,7 +110,18 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
         St[j] = p[j] * Sg[j];
         Sg[j] = St[j] * p_c;
       }
-      if (S && act) {
+      if (DIRECT) {
+        if (S && act && alive) {
+          double *dst = S + n * (int64_t)(J * J) + J * c;  // element (j, c) at j + J*c
+          if (swide) {
+#pragma unroll
+            for (int j = 0; j + 1 < J; j += 2) *reinterpret_cast<double2 *>(dst + j) = make_double2(St[j], St[j + 1]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < J; ++j) dst[j] = St[j];
+          }
+        }
+      } else if (S && act) {
 #pragma unroll
         for (int j = 0; j < J; ++j) sbuf[(r % SR) * J * J + J * c + j] = St[j];  // element (j, c) at j + J*c
       }
@@ -132,7 +145,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
       const double dw = dn * w_c;
 #pragma unroll
       for (int j = 0; j < J; ++j) Sg[j] = fma(w[j], dw, Sg[j]);
-      if ((r + 1) % SR == 0) {
+      if (!DIRECT && (r + 1) % SR == 0) {
         // flush the collected workspace rows (the barrier above made them visible)
         if (S && stored > 0) {
           double *dst     = S + (nt + r + 1 - SR) * (int64_t)(J * J);

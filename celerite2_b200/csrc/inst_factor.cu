@@ -38,7 +38,11 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
       if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       g.carry = sb.states;
     }
-    C2B_LAUNCH("gfactor_apply_kernel", stream, gfactor_apply_kernel<JT><<<grid, kGroupThreads, 0, stream>>>(g));
+    static const bool direct_s = getenv("C2B_S_DIRECT") != nullptr;  // A/B switch, read once
+    if (direct_s && g.S)
+      C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, true><<<grid, kGroupThreads, 0, stream>>>(g)));
+    else
+      C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, false><<<grid, kGroupThreads, 0, stream>>>(g)));
   }
   return C2B_OK;
 }
