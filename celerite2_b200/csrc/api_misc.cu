@@ -8,6 +8,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "host_common.cuh"
 #include "misc.cuh"
 
@@ -47,6 +49,17 @@ void prof_begin(const char *kernel, cudaStream_t s) {
 void prof_end(cudaStream_t s) {
   std::lock_guard<std::mutex> lock(g_prof_mutex);
   if (!g_recs.empty()) cudaEventRecord(g_recs.back().e1, s);
+}
+
+static bool nvtx_on() {
+  static const bool v = getenv("C2B_NVTX") != nullptr;
+  return v;
+}
+void nvtx_push(const char *name) {
+  if (nvtx_on()) nvtxRangePushA(name);
+}
+void nvtx_pop() {
+  if (nvtx_on()) nvtxRangePop();
 }
 
 void set_error(const char *fmt, ...) {

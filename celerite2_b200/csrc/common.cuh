@@ -46,10 +46,20 @@ extern bool g_profile_on;
 extern thread_local const char *g_op;
 void prof_begin(const char *kernel, cudaStream_t s);
 void prof_end(cudaStream_t s);
+// Every C-ABI entry point opens one of these: it names the op for the built-in profile and, when the environment has
+// C2B_NVTX=1, brackets the call with an NVTX range (host-side; shows the entry points above their kernels in a timeline).
+void nvtx_push(const char *name);
+void nvtx_pop();
 struct OpScope {
   const char *prev;
-  explicit OpScope(const char *name) : prev(g_op) { g_op = name; }
-  ~OpScope() { g_op = prev; }
+  explicit OpScope(const char *name) : prev(g_op) {
+    g_op = name;
+    nvtx_push(name);
+  }
+  ~OpScope() {
+    nvtx_pop();
+    g_op = prev;
+  }
 };
 #define C2B_LAUNCH(name, stream, ...)                                                                                                     \
   do {                                                                                                                                    \
