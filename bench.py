@@ -585,12 +585,13 @@ def run_loglike(ctx, name, inp):
         ll_ref, bc_ref, flag = pipe.value_and_grad(co_b, t_b, y_b, d_b)
         raw = res["raw"]
         upd("loglike", ll_gpu[b], ll_ref)
+        g_ref = oracle.get_celerite_matrices_rev(*co_b, t_b, bc_ref, pipe.ba, pipe.bU + pipe.bU2, pipe.bV)
+        # raw["bt"] is the array AFTER the assembly adjoint added its own d/dx term to it (b_x accumulates): compare the total
         for nm, want in (("a", pipe.a), ("U", pipe.U), ("V", pipe.V), ("d", pipe.d), ("W", pipe.W), ("Z", pipe.Z),
                          ("F", pipe.F), ("bY", pipe.bY), ("ba", pipe.ba), ("bV", pipe.bV), ("bU", pipe.bU + pipe.bU2),
-                         ("bt", pipe.bt + pipe.bt2), ("bc", bc_ref)):
+                         ("bt", pipe.bt + pipe.bt2 + g_ref[6]), ("bc", bc_ref)):
             upd(nm, sel(raw[nm]).reshape(want.shape), want)
         upd("S", sel(raw["S"]).reshape(N, -1), pipe.S)
-        g_ref = oracle.get_celerite_matrices_rev(*co_b, t_b, bc_ref, pipe.ba, pipe.bU + pipe.bU2, pipe.bV)
         for nm, want in zip(gp.COEFF_NAMES, g_ref[:6]):
             if want.size:
                 upd("grad_" + nm, sel(res["grads"][nm]), want)

@@ -31,6 +31,10 @@ _SIGS = {
     "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
     "c2b_add_inplace": [_i64, _vp, _vp, _vp],
+    "c2b_term_coefficients": [_i32, _i64, _vp, ctypes.c_double, _i32, _i32, _i32, _i32, _i32] + [_vp] * 6 + [_vp, _vp],
+    "c2b_term_coefficients_rev": [_i32, _i64, _vp, ctypes.c_double, _i32, _i32, _i32, _i32, _i32] + [_vp] * 6 + [_vp, _vp],
+    "c2b_term_product": [_i64, _i32, _i32] + [_vp] * 6 + [_i32, _i32] + [_vp] * 6 + [_vp] * 6 + [_vp],
+    "c2b_term_product_rev": [_i64, _i32, _i32] + [_vp] * 6 + [_i32, _i32] + [_vp] * 6 + [_vp] * 18 + [_vp],
     "c2b_kernel_matrix": [_i64, _i64, _i32, _i32] + [_vp] * 10,
     "c2b_predict_variance": [_i64, _i64, _i32, _i32] + [_vp] * 10 + [_vp, _sz, _vp],
     "c2b_to_dense": [_i64, _i32] + [_vp] * 7,

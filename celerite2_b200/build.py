@@ -22,7 +22,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 WIDTHS_SWEEP = [0, 1, 2, 3, 4, 5, 6, 7, 8, 16]
 WIDTHS_FACTOR = [0, 1, 2, 3, 4, 5, 6, 7, 8, 16]
 UNITS = (
-    [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_noalloc.cu", None), ("api_predict.cu", None)]
+    [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_noalloc.cu", None), ("api_predict.cu", None), ("api_terms.cu", None)]
     + [("inst_sweep.cu", w) for w in WIDTHS_SWEEP]
     + [("inst_factor.cu", w) for w in WIDTHS_FACTOR]
 )

@@ -138,7 +138,16 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
     const int64_t have = batch * (cols > 0 ? cols : 1);
     C                  = have >= target ? 1 : target / have;
     if (C > 8192) C = 8192;
-    const int64_t maxC = N / 64;
+    // shortest chunk worth a summary pass; short series are latency-bound (one warp walks a chunk row by row), so they
+    // are cut finer (c1: N = 1000)
+    static int64_t env_min_rows = -1;
+    if (env_min_rows < 0) {
+      const char *s = getenv("C2B_MIN_CHUNK_ROWS");
+      env_min_rows  = s ? atoll(s) : 0;
+      if (env_min_rows < 0) env_min_rows = 0;
+    }
+    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : 64;
+    const int64_t maxC     = N / min_rows;
     if (C > maxC) C = maxC;
   }
   if (C > N) C = N;

@@ -87,6 +87,37 @@ int c2b_to_dense(int64_t N, int32_t J, const double *t, const double *c, const d
                  void *stream);
 
 /*
+ * Kernel-term algebra on the device: physical hyper-parameters -> coefficient vectors, for a batch of
+ * parameter sets resident on the GPU, with the adjoint maps.  Replaces Term.get_coefficients() of
+ * python/celerite2/terms.py: RealTerm 485-521 (kind 0; params a, c), ComplexTerm 524-569 (kind 1; a, b, c, d),
+ * SHOTerm 604-691 (kind 2; S0, w0, Q; `underdamped` selects the one-complex-term (Q >= 1/2) or two-real-terms form for the
+ * whole batch, `eps` as in the reference), Matern32Term 694-745 (kind 3; sigma, rho; eps), RotationTerm 748-814 (kind 4;
+ * sigma, period, Q0, dQ, f).  params is (batch, P) row-major.  TermSum (terms.py:210-235) is concatenation: every term
+ * writes its own slots [r_off, ..) / [c_off, ..) of coefficient arrays with rows of Jr_total / Jc_total entries.
+ * `bad` (nullable, one int32, caller zeroes it) is set to 1 if a parameter set falls on the other side of Q = 1/2.
+ * The adjoint reads the cotangents of the coefficient arrays (same slots) and overwrites b_params (batch, P).
+ * c2b_term_product: coefficients of the product of two kernels (TermProduct, terms.py:238-300), Jr = Jr1 Jr2,
+ * Jc = Jr1 Jc2 + Jr2 Jc1 + 2 Jc1 Jc2 in the reference's order; _rev overwrites the cotangents of both factors.
+ * TermDiff and TermConvolution (terms.py:304-410) are not provided.
+ */
+int c2b_term_coefficients(int32_t kind, int64_t batch, const double *params, double eps, int32_t underdamped, int32_t Jr_total,
+                          int32_t Jc_total, int32_t r_off, int32_t c_off, double *ar, double *cr, double *ac, double *bc, double *cc,
+                          double *dc, int32_t *bad, void *stream);
+int c2b_term_coefficients_rev(int32_t kind, int64_t batch, const double *params, double eps, int32_t underdamped, int32_t Jr_total,
+                              int32_t Jc_total, int32_t r_off, int32_t c_off, const double *b_ar, const double *b_cr, const double *b_ac,
+                              const double *b_bc, const double *b_cc, const double *b_dc, double *b_params, void *stream);
+int c2b_term_product(int64_t batch, int32_t Jr1, int32_t Jc1, const double *ar1, const double *cr1, const double *ac1, const double *bc1,
+                     const double *cc1, const double *dc1, int32_t Jr2, int32_t Jc2, const double *ar2, const double *cr2,
+                     const double *ac2, const double *bc2, const double *cc2, const double *dc2, double *ar, double *cr, double *ac,
+                     double *bc, double *cc, double *dc, void *stream);
+int c2b_term_product_rev(int64_t batch, int32_t Jr1, int32_t Jc1, const double *ar1, const double *cr1, const double *ac1,
+                         const double *bc1, const double *cc1, const double *dc1, int32_t Jr2, int32_t Jc2, const double *ar2,
+                         const double *cr2, const double *ac2, const double *bc2, const double *cc2, const double *dc2,
+                         const double *b_ar, const double *b_cr, const double *b_ac, const double *b_bc, const double *b_cc,
+                         const double *b_dc, double *g1_ar, double *g1_cr, double *g1_ac, double *g1_bc, double *g1_cc, double *g1_dc,
+                         double *g2_ar, double *g2_cr, double *g2_ac, double *g2_bc, double *g2_cc, double *g2_dc, void *stream);
+
+/*
  * Dense pieces of the predictive distribution, python/celerite2/core.py:52-66,134-150.  The reference
  * builds K* = kernel.get_value(x[:, None] - xs[None, :]) (N x M) in numpy, applies K^-1 to it and takes
  * k(0) - einsum("ij,ij->j", K*, K^-1 K*) (numpy.py:24-25).
