@@ -1,0 +1,35 @@
+#!/bin/bash
+# round-2 second GPU pass (one GPU): full suite, A/B switches, side configurations, ncu launch list + full capture, sanitizer
+mkdir -p gpurun_out
+O=gpurun_out
+timeout 1800 python -m pytest tests -m gpu -q --maxfail=15 > $O/r02b_pytest.log 2>&1; echo "pytest rc=$?" >> $O/r02b_pytest.log
+B="timeout 400 python bench.py --steps 10 --warmup 3"
+export C2B_BENCH_NO_ASSERT=1
+$B --workload c2 > $O/r02b_bench_c2.json 2> $O/r02b_bench_c2.err
+for v in "C2B_S_DIRECT=1" "C2B_SCAN=prefix" "C2B_S_DIRECT=1 C2B_SCAN=prefix" "C2B_SCAN=prefix C2B_TARGET_UNITS=9472" "C2B_SCAN=prefix C2B_TARGET_UNITS=4736" "C2B_TARGET_UNITS=4736" "C2B_TARGET_UNITS=5920"; do
+  tag=$(echo "$v" | tr ' =' '__')
+  env $v $B --workload c2 --no-cpu-baseline > $O/r02b_ab_c2_$tag.json 2> $O/r02b_ab_c2_$tag.err
+done
+for v in "C2B_MIN_CHUNK_ROWS=16" "C2B_MIN_CHUNK_ROWS=32" "C2B_MIN_CHUNK_ROWS=8"; do
+  tag=$(echo "$v" | tr ' =' '__')
+  env $v $B --workload c1 --no-cpu-baseline > $O/r02b_ab_c1_$tag.json 2> $O/r02b_ab_c1_$tag.err
+done
+$B --workload c1 > $O/r02b_bench_c1.json 2> $O/r02b_bench_c1.err
+$B --workload c4 > $O/r02b_bench_c4.json 2> $O/r02b_bench_c4.err
+for v in "C2B_CHUNKS=256" "C2B_CHUNKS=512" "C2B_CHUNKS=2048" "C2B_CHUNKS=512 C2B_SCAN=prefix" "C2B_SCAN=prefix"; do
+  tag=$(echo "$v" | tr ' =' '__')
+  env $v $B --workload c4 --no-cpu-baseline > $O/r02b_ab_c4_$tag.json 2> $O/r02b_ab_c4_$tag.err
+done
+$B --workload c5 > $O/r02b_bench_c5.json 2> $O/r02b_bench_c5.err
+C2B_S_DIRECT=1 $B --workload c5 --no-cpu-baseline > $O/r02b_ab_c5_sdirect.json 2> $O/r02b_ab_c5_sdirect.err
+$B --workload c3 > $O/r02b_bench_c3.json 2> $O/r02b_bench_c3.err
+C2B_S_DIRECT=1 $B --workload c3 --no-cpu-baseline > $O/r02b_ab_c3_sdirect.json 2> $O/r02b_ab_c3_sdirect.err
+$B --workload c3 --batch-per-gpu 14208 --no-cpu-baseline > $O/r02b_ab_c3_wave.json 2> $O/r02b_ab_c3_wave.err
+# reference arm lines (the driver's other arm)
+for w in c2 c1 c4 c5 c3; do timeout 300 python bench.py --impl reference --workload $w --steps 5 --warmup 1 > $O/r02b_ref_$w.json 2> $O/r02b_ref_$w.err; done
+# ncu: launch list of the default bench command, then one full capture of an evaluation's kernels
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/r02b_launches_raw.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/r02b_ncu_launch.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on --launch-skip 140 -c 36 -o $O/r02b_prof python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/r02b_ncu_full.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"gfactor_rev_kernel|gfactor_apply_kernel|gsweep_rev_apply" --launch-skip 8 -c 3 -o $O/r02b_prof_c3 python bench.py --workload c3 --steps 2 --warmup 3 --no-cpu-baseline > $O/r02b_ncu_c3.log 2>&1
+bash dev/sanitize.sh > $O/r02b_sanitize.log 2>&1
+tail -6 $O/r02b_pytest.log
