@@ -114,6 +114,8 @@ def host_inputs(name, rank, world, small=False, batch_per_gpu=None):
         return dict(cfg=cfg, coeffs=cfg["coeffs"], t=t, y=y, diag=diag)
     if name == "c2":
         cfg = wl.config_c2(N=100_000) if small else wl.config_c2()
+        if os.environ.get("C2B_SPLIT_N"):  # development: a longer series for the split-series scaling curve (never the bench line)
+            cfg = wl.config_c2(N=int(os.environ["C2B_SPLIT_N"]))
         t, y, diag = wl.light_curve(cfg["N"], cfg["seed"])  # one series for the whole job (split across ranks when world > 1)
         return dict(cfg=cfg, coeffs=cfg["coeffs"], t=t, y=y, diag=diag)
     if name == "c3":
