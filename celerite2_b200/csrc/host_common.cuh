@@ -70,7 +70,8 @@ static inline Arena sizing_arena() { return Arena((void *)nullptr, (size_t)-1); 
 static inline void take_scan(Arena &ar, int64_t batch, int64_t C, int esize, int ssize, ScanBuffers *sb) {
   Levels lv       = make_levels(C);
   sb->node_stride = lv.total;
-  sb->nodes       = ar.take<double>((size_t)batch * lv.total * esize);
+  // nodes of all series, then one head product per chunk for the blocked fold (fold.cuh; a head is never larger than an element)
+  sb->nodes       = ar.take<double>((size_t)batch * lv.total * esize + (size_t)batch * C * esize);
   sb->states      = ar.take<double>((size_t)batch * lv.total * ssize);
 }
 

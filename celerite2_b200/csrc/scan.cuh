@@ -38,7 +38,7 @@ static inline Levels make_levels(int64_t leaves) {
     cnt = (cnt + 1) / 2;
   }
   lv.nlev  = l;
-  lv.total = off;
+  lv.total = off + 2;  // stride of one series in the scratch arrays: two spare slots behind the levels (fold.cuh's aggregates)
   return lv;
 }
 
@@ -240,6 +240,10 @@ C2B_DEV void slice_out(double *dst, const double *src, int n, int loc, int glob,
 }
 
 
+}  // namespace c2b
+#include "fold.cuh"
+namespace c2b {
+
 // ---- prefix blocks (round 2) ---------------------------------------------------------------------------------------
 // The tree above spends one combine latency per level on the way up AND one apply latency per level on the way down
 // (26 dependent rounds for 7,000 chunks; r01i profile: the scans are 27 % of the c2 step at ~0 bytes moved -- pure
@@ -409,17 +413,22 @@ __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int
 }
 
 
-// Developer switch (environment, read once): C2B_SCAN=tree selects the round-1 block-resident trees, C2B_SCAN=prefix the
-// prefix blocks (A/B runs on the GPU box).  kScanDefaultTree is the default when the variable is unset.
-constexpr bool kScanDefaultTree = true;
-static inline bool scan_use_tree() {
-  static const bool v = [] {
+// Developer switch (environment, read once) for A/B runs on the GPU box: C2B_SCAN names the scan of the chunk summaries,
+//   "tree"   the round-1 block-resident trees for every algebra,
+//   "prefix" prefix blocks for every algebra,
+//   "fold"   the blocked sequential fold (fold.cuh) for the affine algebras, trees for factor's linear-fractional one,
+//   "fold+prefix"  fold for the affine algebras, prefix blocks for factor.
+// Unset: kScanDefault.
+constexpr const char *kScanDefault = "tree";
+static inline const char *scan_mode() {
+  static const char *v = [] {
     const char *e = getenv("C2B_SCAN");
-    if (!e) return kScanDefaultTree;
-    return e[0] == 't' || e[0] == 'T';
+    return (e && e[0]) ? e : kScanDefault;
   }();
   return v;
 }
+static inline bool scan_use_fold() { return strstr(scan_mode(), "fold") != nullptr; }
+static inline bool scan_use_tree() { return strstr(scan_mode(), "prefix") == nullptr; }
 
 // Block size / warps / columns per slice of the prefix-block scan: the largest block whose shared memory (two element
 // buffers, the states, the warps' scratch) lets two CTAs share an SM, else one CTA per SM, narrower slices last.
@@ -520,6 +529,13 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
                            cudaStream_t stream, int mode = 0) {
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
+  if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
+    if (scan_use_fold()) {
+      const Levels lvf = make_levels(leaves);
+      double *heads    = nodes + (size_t)batch * lvf.total * Mon::esize(J, K);  // behind the nodes of all series (take_scan)
+      return run_fold<Mon>(J, K, batch, leaves, lvf.total, nodes, states, heads, init, stream, mode);
+    }
+  }
   if constexpr (Mon::kCoop) {
     if (!scan_use_tree()) return run_pscan<Mon>(J, K, batch, leaves, nodes, states, init, stream, mode);
     // levels per launch / warps per CTA / columns per slice: the largest configuration whose shared memory (sized
@@ -621,6 +637,13 @@ static inline int seg_export_root(int J, int K, int64_t leaves, const double *no
   const Levels lv = make_levels(leaves);
   const int es    = Mon::esize(J, K);
   int64_t root    = lv.off[lv.nlev - 1];
+  if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
+    if (scan_use_fold()) {  // fold: the aggregate of the series sits behind the group aggregates
+      const FoldPlan fp = fold_plan<Mon>(J, K, leaves, lv.total);
+      C2B_CUDA(cudaMemcpyAsync(summary_out, nodes + (fp.C + fp.ng) * es, sizeof(double) * es, cudaMemcpyDeviceToDevice, stream));
+      return C2B_OK;
+    }
+  }
   if constexpr (Mon::kCoop) {
     if (!scan_use_tree()) {  // prefix blocks: the aggregate of the series is the last prefix of the top group
       const PLevels pl = make_plevels(leaves, pscan_plan<Mon>(J, K).BS);
@@ -632,6 +655,9 @@ static inline int seg_export_root(int J, int K, int64_t leaves, const double *no
 }
 template <class Mon>
 static inline int seg_import_state(int J, int K, int64_t leaves, double *states, const double *state_in, cudaStream_t stream) {
+  if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
+    if (scan_use_fold()) return C2B_OK;  // the fold takes the entering state through run_scan's `init`
+  }
   if constexpr (Mon::kCoop) {
     if (!scan_use_tree()) return C2B_OK;  // prefix blocks take the entering state through run_scan's `init`
   }
