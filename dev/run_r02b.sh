@@ -2,7 +2,7 @@
 # round-2 second GPU pass (one GPU): full suite, A/B switches, side configurations, ncu launch list + full capture, sanitizer
 mkdir -p gpurun_out
 O=gpurun_out
-timeout 1800 python -m pytest tests -m gpu -q --maxfail=15 > $O/r02b_pytest.log 2>&1; echo "pytest rc=$?" >> $O/r02b_pytest.log
+timeout 1800 python -m pytest tests -m gpu -q --maxfail=15 --durations=15 > $O/r02b_pytest.log 2>&1; echo "pytest rc=$?" >> $O/r02b_pytest.log
 C2B_SCAN=fold+prefix timeout 1500 python -m pytest tests -m gpu -q --maxfail=15 --deselect tests/test_zz_no_alloc.py > $O/r02b_pytest_fold.log 2>&1; echo "pytest(fold+prefix) rc=$?" >> $O/r02b_pytest.log
 B="timeout 400 python bench.py --steps 10 --warmup 3"
 export C2B_BENCH_NO_ASSERT=1
@@ -29,9 +29,5 @@ C2B_S_DIRECT=1 $B --workload c3 --no-cpu-baseline > $O/r02b_ab_c3_sdirect.json 2
 $B --workload c3 --batch-per-gpu 14208 --no-cpu-baseline > $O/r02b_ab_c3_wave.json 2> $O/r02b_ab_c3_wave.err
 # reference arm lines (the driver's other arm)
 for w in c2 c1 c4 c5 c3; do timeout 300 python bench.py --impl reference --workload $w --steps 5 --warmup 1 > $O/r02b_ref_$w.json 2> $O/r02b_ref_$w.err; done
-# ncu: launch list of the default bench command, then one full capture of an evaluation's kernels
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/r02b_launches_raw.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/r02b_ncu_launch.log 2>&1
-timeout 900 ncu --set full --clock-control none --import-source on --launch-skip 140 -c 36 -o $O/r02b_prof python bench.py --steps 2 --warmup 3 --no-cpu-baseline > $O/r02b_ncu_full.log 2>&1
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"gfactor_rev_kernel|gfactor_apply_kernel|gsweep_rev_apply" --launch-skip 8 -c 3 -o $O/r02b_prof_c3 python bench.py --workload c3 --steps 2 --warmup 3 --no-cpu-baseline > $O/r02b_ncu_c3.log 2>&1
 bash dev/sanitize.sh > $O/r02b_sanitize.log 2>&1
 tail -6 $O/r02b_pytest.log
