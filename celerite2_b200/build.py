@@ -30,7 +30,7 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
 
-_COMMON = ["common.cuh", "monoids.cuh", "coop.cuh", "scan.cuh", "args.cuh", "host_common.cuh"]
+_COMMON = ["common.cuh", "monoids.cuh", "coop.cuh", "scan.cuh", "fold.cuh", "args.cuh", "host_common.cuh"]
 _EXTRA = {
     "api_misc.cu": ["misc.cuh"],
     "inst_sweep.cu": ["sweep.cuh", "group.cuh", "gsweep.cuh"],

@@ -146,7 +146,8 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
       env_min_rows  = s ? atoll(s) : 0;
       if (env_min_rows < 0) env_min_rows = 0;
     }
-    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : 64;
+    // r02b: c1 (N = 1000) 137 us with 64-row chunks, 88 us with 16-row chunks (one warp per 16 chunks, latency-bound rows)
+    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : (N * batch <= 16384 ? 16 : 64);
     const int64_t maxC     = N / min_rows;
     if (C > maxC) C = maxC;
   }

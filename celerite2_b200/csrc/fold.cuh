@@ -40,34 +40,38 @@ struct Fold<AffV<JT>> {
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
     for (int o = tid; o < J * J; o += nt) H[o] = (o / J == o % J) ? 1.0 : 0.0;
   }
-  // sout = M sin + b
-  C2B_DEV static void apply(int tid, int nt, int J, int K, const double *e, const double *sin, double *sout, double *) {
-    const double *b = e + J * J;
+  // Consecutive threads own consecutive ROWS i of a state column (the state is stored j + J k), so they read M down a
+  // column: the kernels keep M TRANSPOSED in shared memory (element (i, j) at j * J + i), or the reads of a warp would sit
+  // J doubles apart (16-way bank conflicts at J = 16: r02b, 5 us per step).  head_slot says where entry r of the head goes.
+  C2B_DEV static int head_slot(int J, int r) { return (r % J) * J + r / J; }
+  // sout = M sin + b            (eT: transposed head, then b)
+  C2B_DEV static void apply(int tid, int nt, int J, int K, const double *eT, const double *sin, double *sout, double *) {
+    const double *b = eT + J * J;
     for (int o = tid; o < J * K; o += nt) {
       const int k = o / J, i = o - k * J;
       double s    = b[o];
 #pragma unroll 4
-      for (int j = 0; j < J; ++j) s = fma(e[i * J + j], sin[j + J * k], s);
+      for (int j = 0; j < J; ++j) s = fma(eT[j * J + i], sin[j + J * k], s);
       sout[o] = s;
     }
   }
-  // Hout = M Hin   (composition "Hin first, then this element")
-  C2B_DEV static void head_step(int tid, int nt, int J, const double *e, const double *Hin, double *Hout) {
+  // Hout = M Hin   (composition "Hin first, then this element"); H row-major
+  C2B_DEV static void head_step(int tid, int nt, int J, const double *eT, const double *Hin, double *Hout) {
     for (int o = tid; o < J * J; o += nt) {
       const int i = o / J, j = o - i * J;
       double s    = 0.0;
 #pragma unroll 4
-      for (int k = 0; k < J; ++k) s = fma(e[i * J + k], Hin[k * J + j], s);
+      for (int k = 0; k < J; ++k) s = fma(eT[k * J + i], Hin[k * J + j], s);
       Hout[o] = s;
     }
   }
-  // out = sloc + H G
-  C2B_DEV static void lift(int tid, int nt, int J, int K, const double *H, const double *sloc, const double *G, double *out, double *) {
+  // out = sloc + H G             (HT: transposed, see head_slot)
+  C2B_DEV static void lift(int tid, int nt, int J, int K, const double *HT, const double *sloc, const double *G, double *out, double *) {
     for (int o = tid; o < J * K; o += nt) {
       const int k = o / J, i = o - k * J;
       double s    = sloc[o];
 #pragma unroll 4
-      for (int j = 0; j < J; ++j) s = fma(H[i * J + j], G[j + J * k], s);
+      for (int j = 0; j < J; ++j) s = fma(HT[j * J + i], G[j + J * k], s);
       out[o] = s;
     }
   }
@@ -82,6 +86,7 @@ struct Fold<DiagV<JT>> {
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
     for (int o = tid; o < J; o += nt) H[o] = 1.0;
   }
+  C2B_DEV static int head_slot(int, int r) { return r; }
   C2B_DEV static void apply(int tid, int nt, int J, int K, const double *e, const double *sin, double *sout, double *) {
     for (int o = tid; o < J * K; o += nt) sout[o] = fma(e[o % J], sin[o], e[J + o]);
   }
@@ -102,6 +107,7 @@ struct Fold<Cong<JT>> {
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
     for (int o = tid; o < J * J; o += nt) H[o] = (o / J == o % J) ? 1.0 : 0.0;
   }
+  C2B_DEV static int head_slot(int, int r) { return r; }  // threads run along rows of M: no conflicts
   // out = 0.5 (R + R^T) + add with R = M^T (G M); two stages through the scratch (T, R)
   C2B_DEV static void sandwich(int tid, int nt, int J, const double *M, const double *G, const double *add, double *out, double *sc) {
     double *T = sc, *R = sc + J * J;
@@ -146,10 +152,13 @@ struct Fold<Cong<JT>> {
 
 }  // namespace c2b
 
+
 // =================================================================================================================
 // kernels (this header is included by scan.cuh after slice_in / slice_out, Levels and kCoopThreadsMax)
 // =================================================================================================================
 namespace c2b {
+
+constexpr int kFoldDepth = 8;  // elements in flight ahead of the walk (a step is shorter than one trip to L2 / HBM)
 
 struct FoldPlan {
   int64_t C;      // chunks per series
@@ -158,7 +167,8 @@ struct FoldPlan {
   int64_t stride; // per-series stride of nodes / states (elements), = Levels::total
   int kb;         // columns per slice
   int nslices;
-  int threads;
+  int threads;    // phases A and B
+  int fthreads;   // phase C: threads per chunk
   size_t smemA, smemC;
 };
 
@@ -166,10 +176,21 @@ struct FoldPlan {
 // states[0, C) carry of every chunk | states[C, C + ng) state entering every group.
 // heads: H[i] of every chunk, (batch, C, hsize), behind the node arrays of all series (host_common.cuh: take_scan).
 
-C2B_DEV void fold_fetch(double *dst, const double *src, int loc, int head, int goff) {
-  // one local element <- global element, 8-byte cp.async per double (the next step's element lands while this one is used)
-  for (int r = threadIdx.x; r < loc; r += blockDim.x) cp_async8(dst + r, src + (r < head ? r : r - head + goff));
+// one local element <- global element, 8-byte cp.async per double; the algebra says where a head entry goes (head_slot)
+template <class Mon>
+C2B_DEV void fold_fetch(int J, double *dst, const double *src, int loc, int head, int hs, int goff) {
+  for (int r = threadIdx.x; r < loc; r += blockDim.x)
+    cp_async8(dst + (r < hs ? Fold<Mon>::head_slot(J, r) : r), src + (r < head ? r : r - head + goff));
 }
+
+// Ring of kFoldDepth element slots.  issue(i) starts the copy of element i of `n` into slot i mod depth (an empty group
+// past the end keeps the group count uniform); ready() makes the oldest outstanding element visible to the CTA.
+struct FoldRing {
+  C2B_DEV static void ready() {
+    cp_async_wait<kFoldDepth - 1>();
+    __syncthreads();
+  }
+};
 
 // phase A: grid.x = batch * ng, grid.y = slices
 template <class Mon>
@@ -188,22 +209,22 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_groups_kernel(int J_, in
   const int64_t b = blockIdx.x / fp.ng, g = blockIdx.x % fp.ng;
   const int64_t first = g * fp.B;
   const int cnt       = (int)(fp.C - first < fp.B ? fp.C - first : fp.B);
-  double *ebuf = fsm;                  // 2 * es
-  double *sbuf = ebuf + 2 * es;        // 2 * ss
-  double *hbuf = sbuf + 2 * ss;        // 2 * hs
-  double *sc   = hbuf + 2 * hs;        // F::scratch
+  double *ebuf = fsm;                        // kFoldDepth * es
+  double *sbuf = ebuf + kFoldDepth * es;     // 2 * ss
+  double *hbuf = sbuf + 2 * ss;              // 2 * hs
+  double *sc   = hbuf + 2 * hs;              // F::scratch
   double *nodes = nodes_all + b * fp.stride * esg, *states = states_all + b * fp.stride * ssg;
   double *heads = heads_all + (b * fp.C + first) * (int64_t)hs;
+  auto issue = [&](int i) {
+    if (i < cnt) fold_fetch<Mon>(J, ebuf + (i % kFoldDepth) * es, nodes + (first + i) * esg, es, eh, hs, ego);
+    cp_async_commit();
+  };
+  for (int i = 0; i < kFoldDepth; ++i) issue(i);
   for (int o = tid; o < ss; o += nt) sbuf[o] = 0.0;
   F::head_identity(tid, nt, J, hbuf);
-  fold_fetch(ebuf, nodes + first * esg, es, eh, ego);
-  cp_async_commit();
   for (int i = 0; i < cnt; ++i) {
-    if (i + 1 < cnt) fold_fetch(ebuf + ((i + 1) & 1) * es, nodes + (first + i + 1) * esg, es, eh, ego);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncthreads();
-    const double *e = ebuf + (i & 1) * es;
+    FoldRing::ready();
+    const double *e = ebuf + (i % kFoldDepth) * es;
     const double *s = sbuf + (i & 1) * ss, *H = hbuf + (i & 1) * hs;
     double *sn = sbuf + ((i + 1) & 1) * ss, *Hn = hbuf + ((i + 1) & 1) * hs;
     // what enters chunk i when the group starts from zero, and the head product of the chunks before it
@@ -213,7 +234,8 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_groups_kernel(int J_, in
       for (int o = tid; o < hs; o += nt) heads[(int64_t)i * hs + o] = H[o];
     F::head_step(tid, nt, J, e, H, Hn);
     F::apply(tid, nt, J, kl, e, s, sn, sc);
-    __syncthreads();
+    __syncthreads();  // the slot is free, the new state and head are complete
+    issue(i + kFoldDepth);
   }
   // the group's aggregate: element = [head product | state reached from zero]
   const double *s = sbuf + (cnt & 1) * ss, *H = hbuf + (cnt & 1) * hs;
@@ -222,7 +244,7 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_groups_kernel(int J_, in
     for (int o = tid; o < hs; o += nt) agg[o] = H[o];
     for (int o = tid; o < sh; o += nt) agg[hs + o] = s[o];  // state head (Cong: B)
   }
-  for (int o = tid + sh; o < ss; o += nt) agg[eh + (o - sh) + (ego - eh)] = s[o];
+  for (int o = tid + sh; o < ss; o += nt) agg[ego + (o - sh)] = s[o];
 }
 
 // phase B: grid.x = batch, grid.y = slices.  States entering the groups from `init` (NULL = zero) when want_states;
@@ -241,26 +263,26 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_top_kernel(int J_, int K
   const int ego = eh + Mon::ecol(J) * k0, sgo = sh + Mon::scol(J) * k0;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int64_t b = blockIdx.x;
-  double *ebuf = fsm;                  // 2 * es
-  double *sbuf = ebuf + 2 * es;        // 2 * ss: chain from init
-  double *zbuf = sbuf + 2 * ss;        // 2 * ss: chain from zero (root)
-  double *hbuf = zbuf + 2 * ss;        // 2 * hs
+  double *ebuf = fsm;                        // kFoldDepth * es
+  double *sbuf = ebuf + kFoldDepth * es;     // 2 * ss: chain from init
+  double *zbuf = sbuf + 2 * ss;              // 2 * ss: chain from zero (root)
+  double *hbuf = zbuf + 2 * ss;              // 2 * hs
   double *sc   = hbuf + 2 * hs;
   double *nodes = nodes_all + b * fp.stride * esg, *states = states_all + b * fp.stride * ssg;
+  const int n = (int)fp.ng;
+  auto issue = [&](int g) {
+    if (g < n) fold_fetch<Mon>(J, ebuf + (g % kFoldDepth) * es, nodes + (fp.C + g) * esg, es, eh, hs, ego);
+    cp_async_commit();
+  };
+  for (int g = 0; g < kFoldDepth; ++g) issue(g);
   for (int o = tid; o < ss; o += nt) {
     sbuf[o] = init ? init[b * ssg + (o < sh ? o : o - sh + sgo)] : 0.0;
     zbuf[o] = 0.0;
   }
   F::head_identity(tid, nt, J, hbuf);
-  fold_fetch(ebuf, nodes + fp.C * esg, es, eh, ego);
-  cp_async_commit();
-  const int n = (int)fp.ng;
   for (int g = 0; g < n; ++g) {
-    if (g + 1 < n) fold_fetch(ebuf + ((g + 1) & 1) * es, nodes + (fp.C + g + 1) * esg, es, eh, ego);
-    cp_async_commit();
-    cp_async_wait<1>();
-    __syncthreads();
-    const double *e = ebuf + (g & 1) * es;
+    FoldRing::ready();
+    const double *e = ebuf + (g % kFoldDepth) * es;
     const int cur = g & 1, nxt = cur ^ 1;
     if (want_states) {
       double *st = states + (fp.C + g) * ssg;
@@ -273,6 +295,7 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_top_kernel(int J_, int K
       F::apply(tid, nt, J, kl, e, zbuf + cur * ss, zbuf + nxt * ss, sc);
     }
     __syncthreads();
+    issue(g + kFoldDepth);
   }
   if (want_root) {
     const double *s = zbuf + (n & 1) * ss, *H = hbuf + (n & 1) * hs;
@@ -281,14 +304,15 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_top_kernel(int J_, int K
       for (int o = tid; o < hs; o += nt) root[o] = H[o];
       for (int o = tid; o < sh; o += nt) root[hs + o] = s[o];
     }
-    for (int o = tid + sh; o < ss; o += nt) root[eh + (o - sh) + (ego - eh)] = s[o];
+    for (int o = tid + sh; o < ss; o += nt) root[ego + (o - sh)] = s[o];
   }
 }
 
-// phase C: one CTA per chunk (grid.x = batch * C, grid.y = slices): carry_i = s_loc[i] + lift(H[i], G[group of i]), in place
+// phase C: carry_i = s_loc[i] + lift(H[i], G[group of i]), in place.  A CTA of 256 threads handles 256 / fthreads chunks
+// (grid.x = batch * ceil(C / chunks per CTA), grid.y = slices); every sub-group runs the same sequence, so the CTA-wide
+// barriers inside `lift` line up.
 template <class Mon>
-__global__ void __launch_bounds__(kFoldMaxThreads) fold_finish_kernel(int J_, int K, FoldPlan fp, double *states_all,
-                                                                     const double *heads_all) {
+__global__ void __launch_bounds__(256) fold_finish_kernel(int J_, int K, FoldPlan fp, double *states_all, const double *heads_all) {
   using F = Fold<Mon>;
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double fsm[];
@@ -298,30 +322,33 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_finish_kernel(int J_, in
   const int ss = Mon::ssize(J, kl), hs = F::hsize(J);
   const int sh = Mon::shead(J);
   const int sgo = sh + Mon::scol(J) * k0;
-  const int tid = threadIdx.x, nt = blockDim.x;
-  const int64_t b = blockIdx.x / fp.C, i = blockIdx.x % fp.C, g = i / fp.B;
-  double *H  = fsm;           // hs
-  double *sl = H + hs;        // ss
-  double *G  = sl + ss;       // ss
-  double *out = G + ss;       // ss
+  const int nt  = fp.fthreads, cpb = blockDim.x / nt;
+  const int sub = threadIdx.x / nt, tid = threadIdx.x - sub * nt;
+  const int64_t per = (fp.C + cpb - 1) / cpb;  // CTAs per series
+  const int64_t b = blockIdx.x / per;
+  const int64_t i = (blockIdx.x % per) * cpb + sub;
+  const bool have = i < fp.C;
+  const int64_t ic = have ? i : fp.C - 1, g = ic / fp.B;
+  const int per_sub = hs + 3 * ss + F::scratch(J, kl);
+  double *H   = fsm + (size_t)sub * per_sub;  // hs
+  double *sl  = H + hs;                       // ss
+  double *G   = sl + ss;                      // ss
+  double *out = G + ss;                       // ss
   double *sc  = out + ss;
   double *states = states_all + b * fp.stride * ssg;
-  const double *hg = heads_all + (b * fp.C + i) * (int64_t)hs;
-  for (int o = tid; o < hs; o += nt) H[o] = hg[o];
+  const double *hg = heads_all + (b * fp.C + ic) * (int64_t)hs;
+  for (int o = tid; o < hs; o += nt) H[F::head_slot(J, o)] = hg[o];
   for (int o = tid; o < ss; o += nt) {
     const int go = o < sh ? o : o - sh + sgo;
-    sl[o]        = states[i * ssg + go];
+    sl[o]        = states[ic * ssg + go];
     G[o]         = states[(fp.C + g) * ssg + go];
   }
   __syncthreads();
   F::lift(tid, nt, J, kl, H, sl, G, out, sc);
   __syncthreads();
-  for (int o = tid; o < ss; o += nt) states[i * ssg + (o < sh ? o : o - sh + sgo)] = out[o];
+  if (have)
+    for (int o = tid; o < ss; o += nt) states[i * ssg + (o < sh ? o : o - sh + sgo)] = out[o];
 }
-
-}  // namespace c2b
-
-namespace c2b {
 
 template <class Mon>
 static inline FoldPlan fold_plan(int J, int K, int64_t leaves, int64_t stride) {
@@ -335,22 +362,25 @@ static inline FoldPlan fold_plan(int J, int K, int64_t leaves, int64_t stride) {
   fp.ng     = (leaves + B - 1) / B;
   fp.stride = stride;
   const int hs = F::hsize(J);
-  auto doubles = [&](int kb, bool top) {
-    return (size_t)2 * Mon::esize(J, kb) + (size_t)(top ? 4 : 2) * Mon::ssize(J, kb) + 2 * hs + F::scratch(J, kb);
+  auto doubles = [&](int kb) {
+    return (size_t)kFoldDepth * Mon::esize(J, kb) + (size_t)4 * Mon::ssize(J, kb) + 2 * hs + F::scratch(J, kb);
   };
   int kb = K;
-  while (kb > 1 && doubles(kb, true) * sizeof(double) > 96 * 1024) kb = (kb + 1) / 2;
+  while (kb > 1 && doubles(kb) * sizeof(double) > 160 * 1024) kb = (kb + 1) / 2;
   const int nsl = (K + kb - 1) / kb;
   kb            = (K + nsl - 1) / nsl;
   fp.kb      = kb;
   fp.nslices = nsl;
-  int work   = Mon::ssize(J, kb) > hs ? Mon::ssize(J, kb) : hs;
-  int th     = (work + 31) / 32 * 32;
+  const int work = Mon::ssize(J, kb) > hs ? Mon::ssize(J, kb) : hs;
+  int th         = (work + 31) / 32 * 32;
   if (th < 64) th = 64;
   if (th > kFoldMaxThreads) th = kFoldMaxThreads;
   fp.threads = th;
-  fp.smemA   = doubles(kb, true) * sizeof(double);
-  fp.smemC   = ((size_t)hs + 3 * Mon::ssize(J, kb) + F::scratch(J, kb)) * sizeof(double);
+  int ft     = 32;
+  while (ft < Mon::ssize(J, kb) && ft < 256) ft *= 2;
+  fp.fthreads = ft;
+  fp.smemA    = doubles(kb) * sizeof(double);
+  fp.smemC    = (size_t)(256 / ft) * ((size_t)hs + 3 * Mon::ssize(J, kb) + F::scratch(J, kb)) * sizeof(double);
   return fp;
 }
 
@@ -373,11 +403,10 @@ static inline int run_fold(int J, int K, int64_t batch, int64_t leaves, int64_t 
   C2B_LAUNCH("fold_top_kernel", stream,
              (fold_top_kernel<Mon><<<dim3((unsigned)batch, ns), fp.threads, fp.smemA, stream>>>(J, K, fp, mode != 1, mode == 1, nodes, states, init)));
   if (mode != 1) {
-    int th = (Mon::ssize(J, fp.kb) + 31) / 32 * 32;
-    if (th < 32) th = 32;
-    if (th > 256) th = 256;
+    const int cpb     = 256 / fp.fthreads;
+    const int64_t per = (fp.C + cpb - 1) / cpb;
     C2B_LAUNCH("fold_finish_kernel", stream,
-               (fold_finish_kernel<Mon><<<dim3((unsigned)(batch * fp.C), ns), th, fp.smemC, stream>>>(J, K, fp, states, heads)));
+               (fold_finish_kernel<Mon><<<dim3((unsigned)(batch * per), ns), 256, fp.smemC, stream>>>(J, K, fp, states, heads)));
   }
   return C2B_OK;
 }
