@@ -52,6 +52,15 @@ def _stale(target, deps):
 
 def build(force=False, verbose_ptxas=False):
     os.makedirs(OBJ, exist_ok=True)
+    # extra compile flags (tuning macros such as -DC2B_MINB_SWEEP=10) apply to EVERY translation unit; a change of flags
+    # rebuilds everything
+    extra = os.environ.get("C2B_NVCC_FLAGS", "").split()
+    stamp = os.path.join(OBJ, "flags.txt")
+    old = open(stamp).read() if os.path.exists(stamp) else ""
+    if old != " ".join(extra):
+        force = True
+    with open(stamp, "w") as f:
+        f.write(" ".join(extra))
     units = list(UNITS)
     missing = [u for (u, _) in units if not os.path.exists(os.path.join(CSRC, u))]
     if missing:
@@ -64,7 +73,7 @@ def build(force=False, verbose_ptxas=False):
     for u, w in units:
         obj = objname(u, w)
         if force or _stale(obj, _deps(u)):
-            cmd = [NVCC] + ARCH + FLAGS + (["-Xptxas", "-v"] if verbose_ptxas else [])
+            cmd = [NVCC] + ARCH + FLAGS + extra + (["-Xptxas", "-v"] if verbose_ptxas else [])
             if w is not None:
                 cmd += ["-DC2B_JT=%d" % w]
             cmd += ["-c", os.path.join(CSRC, u), "-o", obj]

@@ -112,7 +112,7 @@ bool no_group_kernels() {
   return v;
 }
 
-Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
+Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm) {
   Plan pl;
   pl.N     = N;
   pl.batch = batch;
@@ -132,12 +132,12 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J) {
       // one wave of lane-group CTAs, shared by the series of a batch; the 8192 limit is on the chunks of ONE series
       // (the depth of its tree), not on the product
       const int lanes = J <= 2 ? 2 : (J <= 4 ? 4 : (J <= 8 ? 8 : (J <= 16 ? 16 : 32)));
-      target          = (int64_t)sm_count() * 6 * (64 / lanes);
+      target          = (int64_t)sm_count() * ctas_per_sm * (64 / lanes);
     }
     if (env_target > 0) target = env_target;
     const int64_t have = batch * (cols > 0 ? cols : 1);
     C                  = have >= target ? 1 : target / have;
-    if (C > 8192) C = 8192;
+    if (C > 16384) C = 16384;
     // shortest chunk worth a summary pass; short series are latency-bound (one warp walks a chunk row by row), so they
     // are cut finer (c1: N = 1000)
     static int64_t env_min_rows = -1;

@@ -10,6 +10,23 @@
 
 #define C2B_DEV __device__ __forceinline__
 
+// Resident CTAs per SM the lane-group kernels (64 threads each) are compiled for, per kernel family: caps their
+// registers at 65536 / (64 * n) and sizes the chunk plan of the op (make_plan: exactly one wave of CTAs; every op has its
+// own plan, so the families may differ).  r02p profile: at 6 CTAs (3 warps per scheduler) the kernels issue on 40 % of
+// the cycles, one instruction per warp every ~7 cycles: latency-bound, more resident warps is the lever.
+#ifndef C2B_MINB_SWEEP
+#define C2B_MINB_SWEEP 6
+#endif
+#ifndef C2B_MINB_FACTOR
+#define C2B_MINB_FACTOR 6
+#endif
+#ifndef C2B_MINB_FREV
+#define C2B_MINB_FREV 6
+#endif
+#ifndef C2B_FREV_TILE
+#define C2B_FREV_TILE 4  // rows per tile of the factor_rev apply pass (its tiles carry the J x J workspace rows)
+#endif
+
 // Compile-time width JT in 1..8 or 16 gives register arrays and fully unrolled loops; JT == 0 is the
 // run-time-width fallback (J <= C2B_MAX_J, arrays live in local memory).
 template <int JT>
@@ -77,7 +94,7 @@ struct Plan {
   int64_t C;  // chunks per series
   int64_t L;  // points per chunk
 };
-Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J);
+Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm = 6);
 int64_t get_chunk_override();
 bool no_group_kernels();
 

@@ -20,7 +20,7 @@ struct FactorTile {
 // DIRECT: lane c writes its column of a workspace row (J contiguous doubles at offset J*c of the row) straight from
 // registers with 16-byte stores instead of collecting SR rows in shared memory first (A/B switch C2B_S_DIRECT).
 template <int J, bool DIRECT = false>
-__global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorArgs g) {
+__global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;  // groups per CTA
   constexpr int R  = FactorTile<J>::R;
@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(kGroupThreads, 6) gfactor_apply_kernel(FactorA
 // summary: lane c owns column c of A, C, Q (row-major element (j,c)); see factor.cuh for the recurrences
 // tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 template <int J>
-__global__ void __launch_bounds__(kGroupThreads, 6) gfactor_summary_kernel(FactorArgs g) {
+__global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_summary_kernel(FactorArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;
   constexpr int R  = FactorTile<J>::R;

@@ -15,10 +15,10 @@ constexpr int kGroupThreadsR = 64;
 // bc / bt terms (reverse.hpp:47-60), not the recursion of G.
 // tile buffer (rows walked downwards): [S[R*J*J]] U[R*J] W[R*J] bW[R*J] | t[R+2] d[R] bd[R]
 template <int J, bool WRITE>
-__global__ void __launch_bounds__(kGroupThreadsR, 6) gfactor_rev_kernel(FactorRevArgs g) {
+__global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_kernel(FactorRevArgs g) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreadsR / G;
-  constexpr int R  = J <= 7 ? (WRITE ? 4 : 8) : (J <= 8 ? (WRITE ? 2 : 8) : 2);  // static shared memory stays under 48 KB
+  constexpr int R  = J <= 7 ? (WRITE ? C2B_FREV_TILE : 8) : (J <= 8 ? (WRITE ? 2 : 8) : 2);  // static shared memory stays under 48 KB
   constexpr int JE = (J + 1) & ~1;
   constexpr int JJ = WRITE ? J * J : 0;
   constexpr int oU = R * JJ, oW = oU + R * J, oB = oW + R * J, oT = oB + R * J, oD = oT + R + 2, oE = oD + R;

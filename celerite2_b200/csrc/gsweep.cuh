@@ -14,7 +14,7 @@ constexpr int kTileRows = 8;  // rows per staged tile (group.cuh)
 // ---- forward apply -----------------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] | t[R+2] y[R] z_old[R]
 template <int J, bool SOLVE, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_apply_kernel(SweepArgs a) {
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_apply_kernel(SweepAr
 // ---- forward summary, solves: lane q carries column q ----------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] | t[R+2] y[R]; plus one R x J block per group for the propagators of the tile
 template <int J, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(SweepArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_summary_kernel(SweepArgs a) {
   constexpr int G  = GroupOf<J + 1>::G;  // J + 1 columns
   constexpr int GP = kGroupThreadsS / G;
   constexpr int R  = kTileRows;
@@ -217,7 +217,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_summary_kernel(Sweep
 // (general_matmul_lower / upper, forward.hpp:285-392).
 // tile buffer: B[R*J] | t[R+2] y[R]
 template <int J, bool LOWER, bool STORE = false>
-__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_msummary_kernel(SweepArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_msummary_kernel(SweepArgs a) {
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreadsS / G;
   constexpr int R  = kTileRows;
@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_msummary_kernel(Swee
 // ---- reverse summary, matmuls ------------------------------------------------------------------------------------------
 // tile buffer: A[R*J] | t[R+2] bZ[R]
 template <int J, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_msummary_kernel(SweepRevArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_msummary_kernel(SweepRevArgs a) {
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -388,7 +388,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_msummary_kernel(
 // ---- reverse apply -----------------------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] F[R*J] | t[R+2] bZ[R] (Z or Y)[R]
 template <int J, bool SOLVE, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(SweepRevArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_apply_kernel(SweepRevArgs a) {
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -515,7 +515,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_apply_kernel(Swe
 // ---- reverse summary, solves -----------------------------------------------------------------------------------------
 // tile buffer: A[R*J] B[R*J] | t[R+2] bZ[R]; plus the R x J propagator block
 template <int J, bool LOWER>
-__global__ void __launch_bounds__(kGroupThreadsS, 6) gsweep_rev_summary_kernel(SweepRevArgs a) {
+__global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_summary_kernel(SweepRevArgs a) {
   constexpr int G   = GroupOf<J + 1>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
