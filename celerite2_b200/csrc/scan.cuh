@@ -413,22 +413,28 @@ __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int
 }
 
 
-// Developer switch (environment, read once) for A/B runs on the GPU box: C2B_SCAN names the scan of the chunk summaries,
-//   "tree"   the round-1 block-resident trees for every algebra,
-//   "prefix" prefix blocks for every algebra,
-//   "fold"   the blocked sequential fold (fold.cuh) for the affine algebras, trees for factor's linear-fractional one,
-//   "fold+prefix"  fold for the affine algebras, prefix blocks for factor.
-// Unset: kScanDefault.
-constexpr const char *kScanDefault = "tree";
+// Which scan runs (measured on the B200, profiles/r02b_ab_runs.json, r02c_*):
+//   trees         (scan.cuh, round 1)  the default for one right-hand side: 64 us (AffV), 72 us (Cong), 128 us (Lft) at
+//                 C = 7,104, J = 6;
+//   blocked fold  (fold.cuh)           the default for the affine algebras with K > 1: the J x K state makes a tree
+//                 combine a warp-serial J x J x K product (c4: 255 us per sweep), a fold step is one CTA-parallel apply
+//                 (134 us per sweep).  At K = 1 its ~170 steps of ~0.6 us lose to the tree (102 us vs 64 us);
+//   prefix blocks (below)              2.7 % faster than the trees on the c2 step, but their in-place prefixes race between
+//                 column slices; kept as an A/B switch for K = 1 only.
+// C2B_SCAN (environment, read once) overrides: "tree", "prefix", "fold" (every affine scan), "fold+prefix".
 static inline const char *scan_mode() {
   static const char *v = [] {
     const char *e = getenv("C2B_SCAN");
-    return (e && e[0]) ? e : kScanDefault;
+    return (e && e[0]) ? e : "auto";
   }();
   return v;
 }
-static inline bool scan_use_fold() { return strstr(scan_mode(), "fold") != nullptr; }
-static inline bool scan_use_tree() { return strstr(scan_mode(), "prefix") == nullptr; }
+static inline bool scan_use_fold(int K) {
+  if (strstr(scan_mode(), "fold")) return true;
+  if (strstr(scan_mode(), "auto")) return K > 1;
+  return false;
+}
+static inline bool scan_use_tree(int K) { return strstr(scan_mode(), "prefix") == nullptr || K > 1; }
 
 // Block size / warps / columns per slice of the prefix-block scan: the largest block whose shared memory (two element
 // buffers, the states, the warps' scratch) lets two CTAs share an SM, else one CTA per SM, narrower slices last.
@@ -530,14 +536,14 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
-    if (scan_use_fold()) {
+    if (scan_use_fold(K)) {
       const Levels lvf = make_levels(leaves);
       double *heads    = nodes + (size_t)batch * lvf.total * Mon::esize(J, K);  // behind the nodes of all series (take_scan)
       return run_fold<Mon>(J, K, batch, leaves, lvf.total, nodes, states, heads, init, stream, mode);
     }
   }
   if constexpr (Mon::kCoop) {
-    if (!scan_use_tree()) return run_pscan<Mon>(J, K, batch, leaves, nodes, states, init, stream, mode);
+    if (!scan_use_tree(K)) return run_pscan<Mon>(J, K, batch, leaves, nodes, states, init, stream, mode);
     // levels per launch / warps per CTA / columns per slice: the largest configuration whose shared memory (sized
     // for the launch that holds nodes and states) lets two CTAs share an SM
     static const int cand[][2] = {{5, 16}, {5, 8}, {4, 8}, {4, 4}, {3, 4}, {2, 2}, {1, 1}};
@@ -638,14 +644,14 @@ static inline int seg_export_root(int J, int K, int64_t leaves, const double *no
   const int es    = Mon::esize(J, K);
   int64_t root    = lv.off[lv.nlev - 1];
   if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
-    if (scan_use_fold()) {  // fold: the aggregate of the series sits behind the group aggregates
+    if (scan_use_fold(K)) {  // fold: the aggregate of the series sits behind the group aggregates
       const FoldPlan fp = fold_plan<Mon>(J, K, leaves, lv.total);
       C2B_CUDA(cudaMemcpyAsync(summary_out, nodes + (fp.C + fp.ng) * es, sizeof(double) * es, cudaMemcpyDeviceToDevice, stream));
       return C2B_OK;
     }
   }
   if constexpr (Mon::kCoop) {
-    if (!scan_use_tree()) {  // prefix blocks: the aggregate of the series is the last prefix of the top group
+    if (!scan_use_tree(K)) {  // prefix blocks: the aggregate of the series is the last prefix of the top group
       const PLevels pl = make_plevels(leaves, pscan_plan<Mon>(J, K).BS);
       root             = pl.off[pl.ng - 1] + pl.cnt[pl.ng - 1] - 1;
     }
@@ -656,10 +662,10 @@ static inline int seg_export_root(int J, int K, int64_t leaves, const double *no
 template <class Mon>
 static inline int seg_import_state(int J, int K, int64_t leaves, double *states, const double *state_in, cudaStream_t stream) {
   if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
-    if (scan_use_fold()) return C2B_OK;  // the fold takes the entering state through run_scan's `init`
+    if (scan_use_fold(K)) return C2B_OK;  // the fold takes the entering state through run_scan's `init`
   }
   if constexpr (Mon::kCoop) {
-    if (!scan_use_tree()) return C2B_OK;  // prefix blocks take the entering state through run_scan's `init`
+    if (!scan_use_tree(K)) return C2B_OK;  // prefix blocks take the entering state through run_scan's `init`
   }
   const Levels lv = make_levels(leaves);
   const int ss    = Mon::ssize(J, K);
