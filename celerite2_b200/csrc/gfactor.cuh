@@ -31,8 +31,8 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
   constexpr int SR = FactorTile<J>::SR;
   constexpr int SS = GTileStride<G, SR * J * J, 1>::value;
   __shared__ __align__(16) double stile[GP * GS];
-  __shared__ __align__(16) double sprop[GP * R * JE];
-  __shared__ __align__(16) double sxch[GP * 2 * JE];
+  __shared__ __align__(16) double sprop[GP * GPad<G, R * JE>::value];
+  __shared__ __align__(16) double sxch[GP * GPad<G, 2 * JE>::value];
   __shared__ double scc[GP * JE];
   __shared__ __align__(16) double srows[DIRECT ? 2 : GP * SS];  // the tile's S rows, flushed with wide stores once per tile
   const int c          = threadIdx.x & (G - 1);
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
   const double *a = g.a + b * g.N, *U = g.U + b * NJ, *V = g.V + b * NJ;
   double *d = g.d + b * g.N, *W = g.W + b * NJ;
   double *S = g.S ? g.S + b * NJ * J : nullptr;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 2 * JE, *sbuf = srows + (DIRECT ? 0 : gin * SS);
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value, *xch = sxch + gin * GPad<G, 2 * JE>::value, *sbuf = srows + (DIRECT ? 0 : gin * SS);
   const GCopy<G> cp{c};
   const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
@@ -177,8 +177,8 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_summar
   constexpr int TB = (oA + R + 1) & ~1;
   constexpr int GS = GTileStride<G, TB, 2>::value;
   __shared__ __align__(16) double stile[GP * GS];
-  __shared__ __align__(16) double sprop[GP * R * JE];
-  __shared__ __align__(16) double sxch[GP * 4 * JE];
+  __shared__ __align__(16) double sprop[GP * GPad<G, R * JE>::value];
+  __shared__ __align__(16) double sxch[GP * GPad<G, 4 * JE>::value];
   __shared__ double scc[GP * JE];
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
@@ -192,7 +192,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_summar
   const double *t      = g.t + b * g.t_bs;
   const int64_t NJ     = g.N * J;
   const double *a = g.a + b * g.N, *U = g.U + b * NJ, *V = g.V + b * NJ;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 4 * JE;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value, *xch = sxch + gin * GPad<G, 4 * JE>::value;
   const GCopy<G> cp{c};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const double cc = act ? (g.c + b * g.c_bs)[c] : 0.0;

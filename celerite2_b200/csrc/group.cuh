@@ -195,6 +195,16 @@ struct GCopy {
   }
 };
 
+// Per-group scratch arrays (propagators of a tile, exchanged row vectors) need the same treatment as the tiles: the groups
+// of a half-warp (8-byte accesses) or quarter-warp (16-byte accesses) read the same offsets of their own arrays in one
+// instruction, so a per-group stride that is a multiple of 16 doubles puts them on the same banks (r02p: 52 % of the
+// shared-memory wavefronts of the J = 4 factor kernel were conflicts).  Stride = N padded to G doubles modulo 16.
+template <int G, int N>
+struct GPad {
+  // (G = 2 packs 32 groups into a CTA: its arrays stay dense, or the padding alone would exceed the static limit)
+  static constexpr int value = G < 4 ? N : N + ((G % 16) - N % 16 + 16) % 16;
+};
+
 // doubles per group for NBUF tile buffers of TB doubles each, padded like GRing::kStride
 template <int G, int TB, int NBUF>
 struct GTileStride {

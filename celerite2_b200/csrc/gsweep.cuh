@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_summary
   constexpr int TB = (oY + R + 1) & ~1;
   constexpr int GS = GTileStride<G, TB, 2>::value;
   __shared__ __align__(16) double stile[GP * GS];
-  __shared__ __align__(16) double sprop[GP * R * JE];
+  __shared__ __align__(16) double sprop[GP * GPad<G, R * JE>::value];
   __shared__ double scc[GP * JE];
   const int q         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
@@ -136,7 +136,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_summary
   const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
   const double *t     = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *Y = a.Y + b * a.y_bs;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value;
   const GCopy<G> cp{q};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
@@ -526,7 +526,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_sum
   constexpr bool UP = !LOWER;
   constexpr int dir = UP ? 1 : -1;
   __shared__ __align__(16) double stile[GP * GS];
-  __shared__ __align__(16) double sprop[GP * R * JE];
+  __shared__ __align__(16) double sprop[GP * GPad<G, R * JE>::value];
   __shared__ double scc[GP * JE];
   const int q         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
@@ -538,7 +538,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_sum
   const int64_t n1    = has ? (n0 + a.L < a.N ? n0 + a.L : a.N) : n0;
   const double *t     = a.t + b * a.t_bs;
   const double *A = a.A + b * a.N * J, *B = a.B + b * a.N * J, *bZ = a.bZ + b * a.N;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value;
   const GCopy<G> cp{q};
   const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
   const double cc = act ? (a.c + b * a.c_bs)[q] : 0.0;
