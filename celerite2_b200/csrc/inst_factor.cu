@@ -38,7 +38,9 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
       if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       g.carry = sb.states;
     }
-    static const bool direct_s = getenv("C2B_S_DIRECT") != nullptr;  // A/B switch, read once
+    // workspace rows straight from registers (16-byte stores of each lane's column): r02b / r02e, -7 % on the factor
+    // kernels against staging them in shared memory first; C2B_S_STAGED=1 keeps the staged form for A/B runs
+    static const bool direct_s = getenv("C2B_S_STAGED") == nullptr;
     if (direct_s && g.S)
       C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, true><<<grid, kGroupThreads, 0, stream>>>(g)));
     else
