@@ -42,9 +42,18 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-# stdout carries exactly one JSON line: keep NCCL's version banner (printed on stdout at NCCL_DEBUG=VERSION) off it
-if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-    os.environ["NCCL_DEBUG"] = "WARN"
+# stdout carries exactly ONE JSON line.  Libraries write banners to file descriptor 1 behind Python's back (NCCL prints its
+# version there when the first communicator comes up), so the real stdout is set aside for the JSON line and descriptor 1
+# points at stderr for everything else.
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+sys.stdout = sys.stderr
+
+
+def emit(line):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
 
 import numpy as np  # noqa: E402
 
@@ -312,7 +321,7 @@ def run_reference_arm(args):
     }
     if args.workload == "c1":
         line["latency_us"] = dt * 1e6
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # =====================================================================================================================
@@ -847,7 +856,7 @@ def run_ours(args):
     else:
         line = run_loglike(ctx, name, inp)
     if ctx.rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
         if not line["parity"]["ok"]:
             sys.stderr.write("bench.py: PARITY FAILURE: %s\n" % json.dumps(line["parity"]))
     ok = line is None or line["parity"]["ok"]
