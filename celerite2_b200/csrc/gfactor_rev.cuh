@@ -25,8 +25,8 @@ __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_ker
   constexpr int TB = (oE + R + 1) & ~1;
   constexpr int GS = GTileStride<G, TB, 2>::value;
   __shared__ __align__(16) double stile[GP * GS];
-  __shared__ __align__(16) double sprop[GP * GPad<G, R * JE>::value];
-  __shared__ __align__(16) double sxch[GP * GPad<G, 2 * JE>::value];
+  __shared__ __align__(16) double sprop[GP * R * JE];  // (dense: padded, the J = 4 kernels drop from 6 to 5 CTAs per SM, r02f)
+  __shared__ __align__(16) double sxch[GP * 2 * JE];
   __shared__ double scc[GP * JE];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
@@ -43,7 +43,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_ker
   const double *d = g.d + b * g.N, *bd = g.bd + b * g.N;
   double *bt = WRITE ? g.bt + b * g.N : nullptr, *ba = WRITE ? g.ba + b * g.N : nullptr;
   double *bU = WRITE ? g.bU + b * NJ : nullptr, *bV = WRITE ? g.bV + b * NJ : nullptr;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value, *xch = sxch + gin * GPad<G, 2 * JE>::value;
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * R * JE, *xch = sxch + gin * 2 * JE;
   const GCopy<G> cp{c};
   const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(bW)) & 15) == 0);
   const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
