@@ -49,7 +49,7 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
     limit = lib.c2b_noalloc_scratch_limit()
     assert limit == 8 << 20
 
-    primed = False
+    primed = set()
     for name, N, K, seed in (("c2_J6", 20000, 1, 31), ("sum4", 30011, 2, 32), ("c2_J6", 20000, 1, 33)):
         t, c, U, W, Y = _case(name, N, K, seed)
         J = U.shape[1]
@@ -70,9 +70,9 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row():
         _lib.check(lib.c2b_solve_lower_noalloc(N, J, K, 1, tt.data_ptr(), cc.data_ptr(), UU.data_ptr(), WW.data_ptr(), YY.data_ptr(),
                                                Z.data_ptr(), F.data_ptr(), _lib.SHARED_T | _lib.SHARED_C, stream))
         torch.cuda.synchronize()
-        if primed:  # the first call on a device may load the kernels' code; from the second on the free memory must not move
+        if (J, K) in primed:  # the first launch of a kernel may load its code; a repeat of the same shape must not move the free memory
             assert torch.cuda.mem_get_info(dev)[0] == free_before
-        primed = True
+        primed.add((J, K))
         assert relerr(Z.cpu().numpy(), Z_ref.cpu().numpy()) < TOL
         assert relerr(F.cpu().numpy(), F_ref.cpu().numpy()) < TOL
         # and against the CPU oracle, so that a fault shared by both entry points cannot hide
