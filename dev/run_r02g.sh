@@ -1,0 +1,10 @@
+#!/bin/bash
+# one GPU: per-width table, the J = 4 workloads after the factor_rev padding revert, full suite
+mkdir -p gpurun_out
+O=gpurun_out
+timeout 900 python dev/width_table.py > $O/r02g_width.log 2>&1
+export C2B_BENCH_NO_ASSERT=1
+for w in c5 c3 c2; do timeout 400 python bench.py --workload $w --steps 10 --warmup 3 --no-cpu-baseline > $O/r02g_bench_$w.json 2> $O/r02g_bench_$w.err; done
+C2B_SCAN=prefix timeout 400 python bench.py --workload c2 --steps 10 --warmup 3 --no-cpu-baseline > $O/r02g_bench_c2_prefix.json 2> $O/r02g_bench_c2_prefix.err
+timeout 1800 python -m pytest tests -m gpu -q --maxfail=15 > $O/r02g_pytest.log 2>&1; echo "pytest rc=$?" >> $O/r02g_pytest.log
+tail -4 $O/r02g_pytest.log; tail -12 $O/r02g_width.log
