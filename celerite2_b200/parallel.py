@@ -2,14 +2,15 @@
 
 Two ways the path shards:
 
-1. Independent series / hyper-parameter samples: contiguous batch ranges per rank, no data-path collective.
+1. Independent series / hyper-parameter samples / right-hand sides: contiguous ranges per rank, no data-path collective.
    `shard()` gives the range, `gather_rows()` collects the per-series results (a few doubles each) at the end.
 2. One long series over several ranks: every rank owns a contiguous row range and needs the recursion state that
-   enters its first row.  Each rank reduces its range to one chunk summary (the top node of its scan tree),
-   the summaries are all-gathered (a few hundred bytes per rank), and every rank folds the summaries of the ranks
-   before it -- `affine_prefix`, `cong_prefix`, `lft_prefix`, the same algebra as csrc/monoids.cuh, O(world * J^3)
-   host work.  The result is handed to the scan as its initial state.  (The device-side hook is the `init`
-   argument of run_scan in csrc/scan.cuh; the C-ABI plumbing for it is the next step)
+   enters its first row.  The product path does this on the device: `segments.SplitSeries`, the `c2b_*_segment` entry
+   points and `c2b_segment_carry`.
+
+`affine_prefix`, `diag_prefix`, `cong_prefix`, `lft_prefix` below are the same fold written in numpy.  They are TEST
+ALGEBRA: `tests/test_multi_rank_gloo.py` uses them to check, on CPU with world size 2, that folding per-rank summaries
+reproduces the sequential recursion; nothing on the product path calls them.
 """
 import os
 
