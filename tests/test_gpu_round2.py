@@ -259,3 +259,30 @@ def test_graph_replay_survives_larger_eager_calls(env):
         assert torch.equal(again["grads"][nm], g0[nm])
     eager = gp.log_likelihood_and_grad(co, *small)
     assert abs(float(eager["loglike"]) - ll0) <= 1e-13 * abs(ll0)
+
+
+# ---- host entry point, small problems: one packed upload ---------------------------------------------------------------
+@pytest.mark.parametrize("grad", [False, True])
+def test_host_entry_point_packed_upload(env, grad):
+    """N = 1000 (BASELINE config 1): HostLogLikelihood packs t, y, diag and the coefficients into one pinned buffer and
+    uploads them in one copy; results equal the device-resident pipeline and the oracle, on repeated calls with new data."""
+    ops, T, H, torch = env
+    import oracle
+    from celerite2_b200 import gp
+    from celerite2_b200 import workloads as wl
+
+    cfg = wl.config_c1()
+    co = [np.ascontiguousarray(v, dtype=np.float64) for v in cfg["coeffs"]]
+    co_h = [torch.from_numpy(v) for v in co]
+    api = gp.HostLogLikelihood(cfg["N"], [v.shape for v in co_h], torch.device("cuda:0"), grad=grad)
+    assert api._packed_h is not None
+    for seed in (0, 1, 2):
+        t, y, diag = wl.light_curve(cfg["N"], seed)
+        out, status = api(co_h, torch.from_numpy(t), torch.from_numpy(y), torch.from_numpy(diag))
+        assert int(status.max().item()) == 0
+        ll_ref, _ = oracle.RefPipeline(_best_ref(), cfg["N"], len(co[0]), len(co[2]), grad=False).value(co, t, y, diag)
+        assert abs(float(out[0]) - ll_ref) <= TOL * abs(ll_ref)
+        if grad:
+            r = gp.log_likelihood_and_grad([T(v) for v in co], T(t), T(y), T(diag))
+            want = np.concatenate([H(r["loglike"]).reshape(1)] + [H(r["grads"][nm]).reshape(-1) for nm in gp.COEFF_NAMES])
+            assert relerr(out.numpy(), want) < 1e-12
