@@ -4,7 +4,8 @@
 namespace c2b {
 
 static void sizes_factor(int64_t N, int J, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb) {
-  *pl = make_plan(N, batch, 1, J, C2B_MINB_FACTOR);
+  static const int64_t units = env_units("C2B_UNITS_FACTOR");
+  *pl = make_plan(N, batch, 1, J, C2B_MINB_FACTOR, units);
   // a single series gets its (one-node) tree even un-chunked: it may be run as a segment of a longer series
   if (pl->C > 1 || batch == 1) take_scan(ar, batch, pl->C, 3 * J * J, J * J, sb);
 }
@@ -17,7 +18,8 @@ size_t scratch_factor(int64_t N, int J, int64_t batch) {
 }
 
 static void sizes_factor_rev(int64_t N, int J, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb, double **bc_part, double **bt_edge) {
-  *pl = make_plan(N, batch, 1, J, C2B_MINB_FREV);
+  static const int64_t units = env_units("C2B_UNITS_FREV");
+  *pl = make_plan(N, batch, 1, J, C2B_MINB_FREV, units);
   if (pl->C > 1 || batch == 1) take_scan(ar, batch, pl->C, 2 * J * J, J * J, sb);
   *bc_part = ar.take<double>((size_t)batch * pl->C * J);
   *bt_edge = ar.take<double>((size_t)batch * pl->C);

@@ -112,7 +112,13 @@ bool no_group_kernels() {
   return v;
 }
 
-Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm) {
+int64_t env_units(const char *name) {
+  const char *s = getenv(name);
+  const int64_t v = s ? atoll(s) : 0;
+  return v > 0 ? v : 0;
+}
+
+Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm, int64_t units) {
   Plan pl;
   pl.N     = N;
   pl.batch = batch;
@@ -135,9 +141,10 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm) {
       target          = (int64_t)sm_count() * ctas_per_sm * (64 / lanes);
     }
     if (env_target > 0) target = env_target;
+    if (units > 0) target = units;
     const int64_t have = batch * (cols > 0 ? cols : 1);
     C                  = have >= target ? 1 : target / have;
-    if (C > 16384) C = 16384;
+    if (C > 16384 && units <= 0) C = 16384;
     // shortest chunk worth a summary pass; short series are latency-bound (one warp walks a chunk row by row), so they
     // are cut finer (c1: N = 1000)
     static int64_t env_min_rows = -1;
@@ -147,7 +154,11 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm) {
       if (env_min_rows < 0) env_min_rows = 0;
     }
     // r02b: c1 (N = 1000) 137 us with 64-row chunks, 88 us with 16-row chunks (one warp per 16 chunks, latency-bound rows)
-    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : (N * batch <= 16384 ? 16 : 64);
+    // r02g: a rank's share of a split series (N = 125k / 250k): 0.517 / 0.549 ms per evaluation with 64-row chunks, 0.420 /
+    // 0.499 ms with 32-row chunks (16 rows: no faster, and grad_dc leaves the 1e-10 band); from 500k on the one-wave
+    // target decides and the floor is not reached
+    const int64_t pts      = N * batch;
+    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : (pts <= 16384 ? 16 : (pts <= 400000 ? 32 : 64));
     const int64_t maxC     = N / min_rows;
     if (C > maxC) C = maxC;
   }

@@ -4,7 +4,8 @@
 namespace c2b {
 
 static int sizes_sweep(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb) {
-  *pl = make_plan(N, batch, (K + 7) / 8, J, C2B_MINB_SWEEP);  // K columns already supply parallelism: fewer chunks per series
+  static const int64_t units = env_units("C2B_UNITS_SWEEP");
+  *pl = make_plan(N, batch, (K + 7) / 8, J, C2B_MINB_SWEEP, K == 1 ? units : 0);  // K columns already supply parallelism: fewer chunks per series
   if (pl->C > 1 || batch == 1) {
     const int es = solve ? J * J + J * K : J + J * K;
     take_scan(ar, batch, pl->C, es, J * K, sb);
@@ -22,7 +23,8 @@ size_t scratch_sweep(bool solve, int64_t N, int J, int K, int64_t batch) {
 
 static int sizes_sweep_rev(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb, double **bc_part,
                            double **bt_edge) {
-  *pl = make_plan(N, batch, (K + 7) / 8, J, C2B_MINB_SWEEP);  // K columns already supply parallelism: fewer chunks per series
+  static const int64_t units = env_units("C2B_UNITS_SWEEP");
+  *pl = make_plan(N, batch, (K + 7) / 8, J, C2B_MINB_SWEEP, K == 1 ? units : 0);  // K columns already supply parallelism: fewer chunks per series
   if (pl->C > 1 || batch == 1) {
     const int es = solve ? J * J + J * K : J + J * K;
     take_scan(ar, batch, pl->C, es, J * K, sb);

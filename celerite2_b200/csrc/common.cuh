@@ -94,7 +94,8 @@ struct Plan {
   int64_t C;  // chunks per series
   int64_t L;  // points per chunk
 };
-Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm = 6);
+Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm = 6, int64_t units = 0);
+int64_t env_units(const char *name);  // per-family chunk targets from the environment (A/B runs), 0 when unset
 int64_t get_chunk_override();
 bool no_group_kernels();
 
@@ -179,6 +180,49 @@ C2B_DEV void cp_async16(double *smem_dst, const double *gmem_src) {  // both 16-
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
 }
 C2B_DEV void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+
+// ---- bulk copies (TMA engine, no tensor map): one instruction of one lane moves a contiguous run between shared and
+// global memory, outside the load/store pipe.  Sizes are multiples of 16 bytes, both addresses 16-byte aligned.
+// r02h: the lane-group kernels are bound by L1 line-wavefronts (every per-lane 16-byte store of a J x J workspace row
+// touches its own 128-byte line: ~20 cycles per row at J = 6); a bulk store costs the pipe nothing.
+C2B_DEV void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+C2B_DEV void bulk_store(double *gmem_dst, const double *smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst),
+               "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(bytes)
+               : "memory");
+}
+C2B_DEV void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the N most recent bulk groups of this thread have finished READING their shared-memory source
+template <int N>
+C2B_DEV void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+// mbarrier-tracked bulk load into shared memory
+C2B_DEV void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+C2B_DEV void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+C2B_DEV void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)),
+      "r"(parity)
+      : "memory");
+}
+C2B_DEV void bulk_load(double *smem_dst, const double *gmem_src, uint32_t bytes, uint64_t *bar) {
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   (uint32_t)__cvta_generic_to_shared(smem_dst)),
+               "l"(gmem_src), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(bar))
+               : "memory");
+}
 template <int N>
 C2B_DEV void cp_async_wait() {
   asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");

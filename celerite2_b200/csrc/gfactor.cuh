@@ -19,8 +19,13 @@ struct FactorTile {
 // tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 // DIRECT: lane c writes its column of a workspace row (J contiguous doubles at offset J*c of the row) straight from
 // registers with 16-byte stores instead of collecting SR rows in shared memory first (A/B switch C2B_S_DIRECT).
-template <int J, bool DIRECT = false>
+// BULK: the lanes collect BR rows in one of two shared-memory buffers (16-byte stores of their columns) and lane 0 of the
+// group hands the finished buffer to the TMA engine (one bulk store of BR * J * J doubles); needs J even and S 16-byte
+// aligned (the launcher checks), otherwise the DIRECT form runs.
+template <int J, bool DIRECT = false, bool BULK = false>
 __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_kernel(FactorArgs g) {
+  static_assert(!(DIRECT && BULK), "one way of writing the workspace rows");
+  constexpr int BR = 2;  // rows per bulk store
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;  // groups per CTA
   constexpr int R  = FactorTile<J>::R;
@@ -34,7 +39,8 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
   __shared__ __align__(16) double sprop[GP * GPad<G, R * JE>::value];
   __shared__ __align__(16) double sxch[GP * GPad<G, 2 * JE>::value];
   __shared__ double scc[GP * JE];
-  __shared__ __align__(16) double srows[DIRECT ? 2 : GP * SS];  // the tile's S rows, flushed with wide stores once per tile
+  constexpr int BS = GTileStride<G, 2 * BR * J * J, 1>::value;
+  __shared__ __align__(16) double srows[DIRECT ? 2 : (BULK ? GP * BS : GP * SS)];  // S rows on their way out
   const int c          = threadIdx.x & (G - 1);
   const int gin        = threadIdx.x / G;
   const int64_t unit   = (int64_t)blockIdx.x * GP + gin;
@@ -49,7 +55,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
   const double *a = g.a + b * g.N, *U = g.U + b * NJ, *V = g.V + b * NJ;
   double *d = g.d + b * g.N, *W = g.W + b * NJ;
   double *S = g.S ? g.S + b * NJ * J : nullptr;
-  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value, *xch = sxch + gin * GPad<G, 2 * JE>::value, *sbuf = srows + (DIRECT ? 0 : gin * SS);
+  double *gbuf = stile + gin * GS, *pb = sprop + gin * GPad<G, R * JE>::value, *xch = sxch + gin * GPad<G, 2 * JE>::value, *sbuf = srows + (DIRECT ? 0 : gin * (BULK ? BS : SS));
   const GCopy<G> cp{c};
   const bool wide  = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(U) | reinterpret_cast<uintptr_t>(V)) & 15) == 0);
   const bool swide = (J % 2 == 0) && ((reinterpret_cast<uintptr_t>(S) & 15) == 0);
@@ -74,10 +80,11 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
       const int rows   = cnt - k * R < R ? cnt - k * R : R;
       const int64_t lo = n0 + (int64_t)k * R;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb, U + lo * J, rows * J, wide);
-      cp.run(tb + oV, V + lo * J, rows * J, wide);
-      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.tmin, g.tmax);
-      cp.run(tb + oA, a + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, g.tmin, g.tmax);
+      cp.template vec<R * J>(tb, U + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oV, V + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT, t, lo - 1, rows + 2, g.tmin, g.tmax, fast);
+      cp.template sca<R>(tb + oA, a + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -121,11 +128,18 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
             for (int j = 0; j < J; ++j) dst[j] = St[j];
           }
         }
+      } else if (BULK) {
+        if (S && act) {
+          double *dst = sbuf + ((r / BR) & 1) * (BR * J * J) + (r % BR) * J * J + J * c;
+#pragma unroll
+          for (int j = 0; j + 1 < J; j += 2) *reinterpret_cast<double2 *>(dst + j) = make_double2(St[j], St[j + 1]);
+        }
+        if ((r + 1) % BR == 0) fence_proxy_async_smem();  // my rows of the buffer, before the barrier below
       } else if (S && act) {
 #pragma unroll
         for (int j = 0; j < J; ++j) sbuf[(r % SR) * J * J + J * c + j] = St[j];  // element (j, c) at j + J*c
       }
-      if (alive) stored = r % SR + 1;
+      if (alive) stored = r % (BULK ? BR : SR) + 1;
       double tmp = 0.0;
 #pragma unroll
       for (int j = 0; j < J; ++j) tmp = fma(u[j], Sg[j], tmp);
@@ -135,7 +149,9 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
         if (c == 0) record_failure(g.status ? g.status + b : nullptr, n);
         alive = false;  // forward.hpp:128: later rows stay untouched (lanes keep participating in the barriers)
       }
-      const double w_c = (v_c - tmp) / dn;
+      // lanes without a column divide 1 by d: a zero numerator sends the whole warp through the slow path of the division
+      // on EVERY row (r02j: 27 % of the kernel's instructions at J = 6)
+      const double w_c = (act ? v_c - tmp : 1.0) / dn;
       if (alive && act) W[n * J + c] = w_c;
       double *xw = xch + (r & 1) * JE;
       if (c < J) xw[c] = w_c;
@@ -145,7 +161,19 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
       const double dw = dn * w_c;
 #pragma unroll
       for (int j = 0; j < J; ++j) Sg[j] = fma(w[j], dw, Sg[j]);
-      if (!DIRECT && (r + 1) % SR == 0) {
+      if (BULK && (r + 1) % BR == 0) {
+        // the barrier after the exchange of w made the buffer's rows visible; rows past a failure stay unwritten
+        if (c == 0) {
+          if (S && stored > 0) {
+            bulk_store(S + (nt + r + 1 - BR) * (int64_t)(J * J), sbuf + ((r / BR) & 1) * (BR * J * J), (uint32_t)(stored * J * J * sizeof(double)));
+          }
+          bulk_commit();
+          bulk_wait_read<1>();  // the other buffer (handed over BR rows ago) may be written again
+        }
+        stored = 0;
+        __syncwarp();
+      }
+      if (!DIRECT && !BULK && (r + 1) % SR == 0) {
         // flush the collected workspace rows (the barrier above made them visible)
         if (S && stored > 0) {
           double *dst     = S + (nt + r + 1 - SR) * (int64_t)(J * J);
@@ -163,6 +191,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
     __syncwarp();
     issue(k + 2);
   }
+  if (BULK && c == 0) bulk_wait_read<0>();  // shared memory must outlive the engine's reads
 }
 
 // summary: lane c owns column c of A, C, Q (row-major element (j,c)); see factor.cuh for the recurrences
@@ -215,10 +244,11 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_summar
       const int rows   = cnt - k * R < R ? cnt - k * R : R;
       const int64_t lo = n0 + (int64_t)k * R;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb, U + lo * J, rows * J, wide);
-      cp.run(tb + oV, V + lo * J, rows * J, wide);
-      cp.run_t(tb + oT, t, lo - 1, rows + 2, g.tmin, g.tmax);
-      cp.run(tb + oA, a + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, g.tmin, g.tmax);
+      cp.template vec<R * J>(tb, U + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oV, V + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT, t, lo - 1, rows + 2, g.tmin, g.tmax, fast);
+      cp.template sca<R>(tb + oA, a + lo, rows, fast);
     }
     cp_async_commit();
   };

@@ -14,8 +14,11 @@ constexpr int kGroupThreadsR = 64;
 // holding row k) through the chunk (summary).  The summary never needs the workspace S: S enters only bU and the
 // bc / bt terms (reverse.hpp:47-60), not the recursion of G.
 // tile buffer (rows walked downwards): [S[R*J*J]] U[R*J] W[R*J] bW[R*J] | t[R+2] d[R] bd[R]
-template <int J, bool WRITE>
+// BULK (apply pass, J even, S 16-byte aligned): the workspace rows of a tile, one contiguous run of R * J * J doubles, come
+// in by one bulk copy of the TMA engine per group and tile (mbarrier-tracked) instead of R * J * J / 2 16-byte cp.async.
+template <int J, bool WRITE, bool BULK = false>
 __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_kernel(FactorRevArgs g) {
+  static_assert(!BULK || (WRITE && J % 2 == 0), "bulk loads are for the workspace rows of the apply pass");
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreadsR / G;
   constexpr int R  = J <= 7 ? (WRITE ? C2B_FREV_TILE : 8) : (J <= 8 ? (WRITE ? 2 : 8) : 2);  // static shared memory stays under 48 KB
@@ -28,8 +31,17 @@ __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_ker
   __shared__ __align__(16) double sprop[GP * R * JE];  // (dense: padded, the J = 4 kernels drop from 6 to 5 CTAs per SM, r02f)
   __shared__ __align__(16) double sxch[GP * 2 * JE];
   __shared__ double scc[GP * JE];
+  __shared__ uint64_t sbar[BULK ? GP * 2 : 1];
   const int c         = threadIdx.x & (G - 1);
   const int gin       = threadIdx.x / G;
+  if (BULK) {
+    if (c == 0) {
+      mbar_init(sbar + gin * 2, 1);
+      mbar_init(sbar + gin * 2 + 1, 1);
+      fence_proxy_async_smem();
+    }
+    __syncwarp();
+  }
   const int64_t unit  = (int64_t)blockIdx.x * GP + gin;
   const bool has      = unit < g.batch * g.C;
   const bool act      = has && c < J;
@@ -77,13 +89,22 @@ __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_ker
       const int64_t lo = n1 - (int64_t)k * R - rows;
       const int pad    = R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      if (WRITE) cp.run(tb + pad * J * J, S + lo * (int64_t)(J * J), rows * J * J, swide);
-      cp.run(tb + oU + pad * J, U + lo * J, rows * J, wide);
-      cp.run(tb + oW + pad * J, W + lo * J, rows * J, wide);
-      cp.run(tb + oB + pad * J, bW + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, g.tmin, g.tmax);
-      cp.run(tb + oD + pad, d + lo, rows, false);
-      cp.run(tb + oE + pad, bd + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, g.tmin, g.tmax);
+      if (BULK) {
+        if (c == 0) {
+          const uint32_t bytes = (uint32_t)(rows * J * J * sizeof(double));
+          mbar_expect_tx(sbar + gin * 2 + (k & 1), bytes);
+          bulk_load(tb + pad * J * J, S + lo * (int64_t)(J * J), bytes, sbar + gin * 2 + (k & 1));
+        }
+      } else if (WRITE) {
+        cp.template vec<R * J * J>(tb + pad * J * J, S + lo * (int64_t)(J * J), rows * J * J, swide, fast);
+      }
+      cp.template vec<R * J>(tb + oU + pad * J, U + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oW + pad * J, W + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oB + pad * J, bW + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, g.tmin, g.tmax, fast);
+      cp.template sca<R>(tb + oD + pad, d + lo, rows, fast);
+      cp.template sca<R>(tb + oE + pad, bd + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -91,6 +112,7 @@ __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_ker
   issue(1);
   for (int k = 0; k < ttrips; ++k) {
     cp_async_wait<1>();
+    if (BULK && k < ntile) mbar_wait(sbar + gin * 2 + (k & 1), (uint32_t)((k >> 1) & 1));
     __syncwarp();
     const double *tb = gbuf + (k & 1) * TB;
     const int rows   = cnt - k * R < R ? (cnt - k * R > 0 ? cnt - k * R : 0) : R;

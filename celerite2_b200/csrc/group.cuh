@@ -183,6 +183,48 @@ struct GCopy {
       for (int e = c; e < cnt; e += G) cp_async8(dst + e, src + e);
     }
   }
+  // ---- full tiles (r02j: the copy loops with run-time counts and the clamped time stamps below were 10 - 25 % of the
+  // instructions of every lane-group kernel; all but the first and last tile of a chunk take this path) -----------------
+  // a full tile of R rows starting at row lo whose time stamps lo-1 .. lo+R exist
+  template <int R>
+  C2B_DEV static bool full_tile(int rows, int64_t lo, int64_t tmin, int64_t tmax) {
+    return rows == R && lo - 1 >= tmin && lo + R <= tmax;
+  }
+  // CNT doubles (even), dst and src 16-byte aligned
+  template <int CNT>
+  C2B_DEV void full16(double *dst, const double *src) const {
+    static_assert(CNT % 2 == 0, "16-byte copies move pairs");
+#pragma unroll
+    for (int e0 = 0; e0 < CNT; e0 += 2 * G) {
+      const int e = e0 + 2 * c;
+      if (e0 + 2 * G <= CNT || e < CNT) cp_async16(dst + e, src + e);
+    }
+  }
+  template <int CNT>
+  C2B_DEV void full8(double *dst, const double *src) const {
+#pragma unroll
+    for (int e0 = 0; e0 < CNT; e0 += G) {
+      const int e = e0 + c;
+      if (e0 + G <= CNT || e < CNT) cp_async8(dst + e, src + e);
+    }
+  }
+  // rows of J-vectors (CNT = doubles of a full tile), scalars per row, time stamps: `fast` = full_tile
+  template <int CNT>
+  C2B_DEV void vec(double *dst, const double *src, int cnt, bool wide, bool fast) const {
+    if (fast && wide) {
+      if constexpr (CNT % 2 == 0) full16<CNT>(dst, src); else run(dst, src, cnt, wide);
+    } else {
+      run(dst, src, cnt, wide);
+    }
+  }
+  template <int CNT>
+  C2B_DEV void sca(double *dst, const double *src, int cnt, bool fast) const {
+    if (fast) full8<CNT>(dst, src); else run(dst, src, cnt, false);
+  }
+  template <int CNT>
+  C2B_DEV void tim(double *dst, const double *t, int64_t first, int cnt, int64_t lo, int64_t hi, bool fast) const {
+    if (fast) full8<CNT>(dst, t + first); else run_t(dst, t, first, cnt, lo, hi);
+  }
   // time stamps with one neighbour on either side: dst[e] = t[clamp(first + e, lo, hi)], e < cnt, [lo, hi] = [0, N-1]
   // for a whole series.  The clamp makes dt = 0 (propagator exactly 1) at the two ends of the series, which is what
   // the recursions want there; a segment of a longer series has a real neighbour at -1 and / or N instead.

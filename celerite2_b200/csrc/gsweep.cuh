@@ -61,11 +61,12 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_apply_k
       const int64_t lo = LOWER ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
       const int pad    = LOWER ? 0 : R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
-      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
-      cp.run(tb + oY + pad, Y + lo, rows, false);
-      if (!SOLVE) cp.run(tb + oZ + pad, Z + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, a.tmin, a.tmax);
+      cp.template vec<R * J>(tb + pad * J, A + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oB + pad * J, B + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax, fast);
+      cp.template sca<R>(tb + oY + pad, Y + lo, rows, fast);
+      if (!SOLVE) cp.template sca<R>(tb + oZ + pad, Z + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -156,10 +157,11 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_summary
       const int64_t lo = LOWER ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
       const int pad    = LOWER ? 0 : R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
-      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
-      cp.run(tb + oY + pad, Y + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, a.tmin, a.tmax);
+      cp.template vec<R * J>(tb + pad * J, A + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oB + pad * J, B + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax, fast);
+      cp.template sca<R>(tb + oY + pad, Y + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -263,9 +265,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_msummar
       const int64_t lo = LOWER ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
       const int pad    = LOWER ? 0 : R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
-      cp.run(tb + oY + pad, Y + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, a.tmin, a.tmax);
+      cp.template vec<R * J>(tb + pad * J, B + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax, fast);
+      cp.template sca<R>(tb + oY + pad, Y + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -345,9 +348,10 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_msu
       const int64_t lo = UP ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
       const int pad    = UP ? 0 : R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
-      cp.run(tb + oZ + pad, bZ + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, a.tmin, a.tmax);
+      cp.template vec<R * J>(tb + pad * J, A + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax, fast);
+      cp.template sca<R>(tb + oZ + pad, bZ + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -437,12 +441,13 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_app
       const int64_t lo = UP ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
       const int pad    = UP ? 0 : R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
-      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run(tb + oF + pad * J, F + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
-      cp.run(tb + oZ + pad, bZ + lo, rows, false);
-      cp.run(tb + oY + pad, ZY + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, a.tmin, a.tmax);
+      cp.template vec<R * J>(tb + pad * J, A + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oB + pad * J, B + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oF + pad * J, F + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax, fast);
+      cp.template sca<R>(tb + oZ + pad, bZ + lo, rows, fast);
+      cp.template sca<R>(tb + oY + pad, ZY + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -558,10 +563,11 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_sum
       const int64_t lo = UP ? n0 + (int64_t)k * R : n1 - (int64_t)k * R - rows;
       const int pad    = UP ? 0 : R - rows;
       double *tb       = gbuf + (k & 1) * TB;
-      cp.run(tb + pad * J, A + lo * J, rows * J, wide);
-      cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
-      cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
-      cp.run(tb + oZ + pad, bZ + lo, rows, false);
+      const bool fast   = GCopy<G>::template full_tile<R>(rows, lo, a.tmin, a.tmax);
+      cp.template vec<R * J>(tb + pad * J, A + lo * J, rows * J, wide, fast);
+      cp.template vec<R * J>(tb + oB + pad * J, B + lo * J, rows * J, wide, fast);
+      cp.template tim<R + 2>(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax, fast);
+      cp.template sca<R>(tb + oZ + pad, bZ + lo, rows, fast);
     }
     cp_async_commit();
   };
@@ -649,12 +655,8 @@ __host__ __device__ inline size_t csweep_smem_doubles(int yw) {
   return (size_t)2 * tb + R * J + J + R;
 }
 
-// CPT columns per thread: the row's A / B / propagator vectors are 3 J doubles of shared-memory reads per thread and row,
-// against 3 J multiply-adds per column -- the load/store pipe, not the FP64 pipe, was the busy unit with one column per
-// thread (r02p: c4 at 8 % of the HBM roofline); two columns per thread halve the reads per multiply-add and give every
-// thread two independent dependency chains.
-template <int J, bool LOWER, bool SUMMARY, int CPT = 1>
-__global__ void __launch_bounds__(kColThreads / CPT, 2) csweep_tile_kernel(SweepArgs a) {
+template <int J, bool LOWER, bool SUMMARY>
+__global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a) {
   constexpr int R  = kTileRows;
   constexpr int oB = R * J, oT = 2 * R * J, oY = oT + ((R + 2 + 1) & ~1);
   extern __shared__ __align__(16) double cs_smem[];
@@ -664,8 +666,7 @@ __global__ void __launch_bounds__(kColThreads / CPT, 2) csweep_tile_kernel(Sweep
   const int64_t n0     = chunk * a.L;
   const int64_t n1     = n0 + a.L < a.N ? n0 + a.L : a.N;
   const int ncol       = SUMMARY ? J + a.K : a.K;
-  const int span       = NT * CPT;                   // columns one pass of the CTA covers
-  const int yw         = span < a.K ? span : a.K;    // widest slice of Y a column group can need
+  const int yw         = NT < a.K ? NT : a.K;  // widest slice of Y a column group can need
   const int TB         = oY + R * yw;
   double *pb           = cs_smem + 2 * TB;
   double *csm          = pb + R * J;
@@ -684,29 +685,23 @@ __global__ void __launch_bounds__(kColThreads / CPT, 2) csweep_tile_kernel(Sweep
   const int ntile = (cnt + R - 1) / R;
   constexpr int dir = LOWER ? 1 : -1;
   const int64_t nf  = LOWER ? n0 : n1 - 1;
-  for (int q0 = 0; q0 < ncol; q0 += span) {
-    // my columns: q0 + CPT tid + i
-    bool have[CPT], basis[CPT];
-    int kcol[CPT];
-    double Fk[CPT][J];
-#pragma unroll
-    for (int i = 0; i < CPT; ++i) {
-      const int q = q0 + CPT * tid + i;
-      have[i]     = q < ncol;
-      basis[i]    = SUMMARY && q < J;
-      kcol[i]     = SUMMARY ? q - J : q;  // real column index
-#pragma unroll
-      for (int j = 0; j < J; ++j) Fk[i][j] = (basis[i] && j == q) ? 1.0 : 0.0;
-      if (!SUMMARY && a.carry && have[i]) {
-        const double *st = a.carry + (b * a.node_stride + leaf) * (int64_t)(J * a.K) + (int64_t)J * kcol[i];
-#pragma unroll
-        for (int j = 0; j < J; ++j) Fk[i][j] = st[j];
-      }
-    }
+  for (int q0 = 0; q0 < ncol; q0 += NT) {
+    const int q      = q0 + tid;  // my column
+    const bool have  = q < ncol;
+    const bool basis = SUMMARY && q < J;
+    const int k      = SUMMARY ? q - J : q;  // real column index
     // real columns of this group: [kc0, kc0 + kw)
     const int kc0 = SUMMARY ? (q0 > J ? q0 - J : 0) : q0;
-    const int kc1 = SUMMARY ? (q0 + span - J < a.K ? q0 + span - J : a.K) : (q0 + span < a.K ? q0 + span : a.K);
+    const int kc1 = SUMMARY ? (q0 + NT - J < a.K ? q0 + NT - J : a.K) : (q0 + NT < a.K ? q0 + NT : a.K);
     const int kw  = kc1 > kc0 ? kc1 - kc0 : 0;
+    double Fk[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) Fk[j] = (basis && j == q) ? 1.0 : 0.0;
+    if (!SUMMARY && a.carry && have) {
+      const double *st = a.carry + (b * a.node_stride + leaf) * (int64_t)(J * a.K) + (int64_t)J * k;
+#pragma unroll
+      for (int j = 0; j < J; ++j) Fk[j] = st[j];
+    }
     auto issue = [&](int kt) {
       if (kt < ntile) {
         const int rows   = cnt - kt * R < R ? cnt - kt * R : R;
@@ -737,55 +732,45 @@ __global__ void __launch_bounds__(kColThreads / CPT, 2) csweep_tile_kernel(Sweep
       const int64_t nt = nf + (int64_t)dir * kt * R;  // first row of the tile in visiting order
       if (zdiv && tid < rows) dinv[tid] = 1.0 / zdiv[nt + dir * tid];
       __syncthreads();
-      if (have[0]) {
+      if (have) {
 #pragma unroll 2
         for (int r = 0; r < R; ++r) {
           if (r < rows) {
             const int s     = LOWER ? r : R - 1 - r;
             const int64_t n = nt + dir * r;
+            if (F) {
+#pragma unroll
+              for (int j = 0; j < J; ++j) F[n * (int64_t)J * a.K + (int64_t)J * k + j] = Fk[j];  // (j, k) at j + J*k
+            }
             double p[J], av[J], bv[J];
             lds_row<J>(pb + r * J, p);
             lds_row<J>(tb + s * J, av);
+            double sm = 0.0;
+#pragma unroll
+            for (int j = 0; j < J; ++j) {
+              Fk[j] = p[j] * Fk[j];
+              sm    = fma(av[j], Fk[j], sm);
+            }
+            const double y = basis ? 0.0 : tb[oY + s * yw + (k - kc0)];
+            const double z = y - sm;
+            if (!SUMMARY) Z[n * (int64_t)a.K + k] = zdiv ? z * dinv[r] : z;
             lds_row<J>(tb + oB + s * J, bv);
 #pragma unroll
-            for (int i = 0; i < CPT; ++i) {
-              if (!have[i]) continue;
-              const int k = kcol[i];
-              if (F) {
-#pragma unroll
-                for (int j = 0; j < J; ++j) F[n * (int64_t)J * a.K + (int64_t)J * k + j] = Fk[i][j];  // (j, k) at j + J*k
-              }
-              double sm = 0.0;
-#pragma unroll
-              for (int j = 0; j < J; ++j) {
-                Fk[i][j] = p[j] * Fk[i][j];
-                sm       = fma(av[j], Fk[i][j], sm);
-              }
-              const double y = basis[i] ? 0.0 : tb[oY + s * yw + (k - kc0)];
-              const double z = y - sm;
-              if (!SUMMARY) Z[n * (int64_t)a.K + k] = zdiv ? z * dinv[r] : z;
-#pragma unroll
-              for (int j = 0; j < J; ++j) Fk[i][j] = fma(bv[j], z, Fk[i][j]);
-            }
+            for (int j = 0; j < J; ++j) Fk[j] = fma(bv[j], z, Fk[j]);
           }
         }
       }
       __syncthreads();
       issue(kt + 2);
     }
-    if (SUMMARY) {
+    if (SUMMARY && have) {
       double *e = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J * J + J * a.K);
+      if (basis) {
 #pragma unroll
-      for (int i = 0; i < CPT; ++i) {
-        if (!have[i]) continue;
-        const int q = q0 + CPT * tid + i;
-        if (basis[i]) {
+        for (int j = 0; j < J; ++j) e[j * J + q] = Fk[j];
+      } else {
 #pragma unroll
-          for (int j = 0; j < J; ++j) e[j * J + q] = Fk[i][j];
-        } else {
-#pragma unroll
-          for (int j = 0; j < J; ++j) e[J * J + j + J * kcol[i]] = Fk[i][j];
-        }
+        for (int j = 0; j < J; ++j) e[J * J + j + J * k] = Fk[j];
       }
     }
   }

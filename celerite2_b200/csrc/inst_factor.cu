@@ -41,6 +41,14 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
     // workspace rows straight from registers (16-byte stores of each lane's column): r02b / r02e, -7 % on the factor
     // kernels against staging them in shared memory first; C2B_S_STAGED=1 keeps the staged form for A/B runs
     static const bool direct_s = getenv("C2B_S_STAGED") == nullptr;
+    // C2B_S_BULK=1: rows collected in shared memory and written by the TMA engine (bulk stores), see gfactor.cuh
+    static const bool bulk_s = getenv("C2B_S_BULK") != nullptr && atoi(getenv("C2B_S_BULK")) != 0;
+    if constexpr (JT % 2 == 0) {
+      if (bulk_s && g.S && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
+        C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, false, true><<<grid, kGroupThreads, 0, stream>>>(g)));
+        return C2B_OK;
+      }
+    }
     if (direct_s && g.S)
       C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, true><<<grid, kGroupThreads, 0, stream>>>(g)));
     else
@@ -100,7 +108,16 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
       if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       g.carry = sb.states;
     }
-    C2B_LAUNCH("gfactor_rev_apply_kernel", stream, gfactor_rev_kernel<JT, true><<<grid, kGroupThreadsR, 0, stream>>>(g));
+    // C2B_S_BULK=1: workspace rows of a tile by one bulk copy (gfactor_rev.cuh)
+    static const bool bulk_s = getenv("C2B_S_BULK") != nullptr && atoi(getenv("C2B_S_BULK")) != 0;
+    bool launched            = false;
+    if constexpr (JT % 2 == 0) {
+      if (bulk_s && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
+        C2B_LAUNCH("gfactor_rev_apply_kernel", stream, (gfactor_rev_kernel<JT, true, true><<<grid, kGroupThreadsR, 0, stream>>>(g)));
+        launched = true;
+      }
+    }
+    if (!launched) C2B_LAUNCH("gfactor_rev_apply_kernel", stream, gfactor_rev_kernel<JT, true><<<grid, kGroupThreadsR, 0, stream>>>(g));
     C2B_LAUNCH("rev_finalize_kernel", stream,
                rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
     if (phase == 2 && g.seg.edge_out)

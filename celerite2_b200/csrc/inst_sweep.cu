@@ -116,33 +116,24 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   if constexpr (JT > 0 && SOLVE) {
-    // two columns per thread from 32 right-hand sides on (C2B_CPT=1 keeps one column per thread for A/B runs)
-    static const bool one_col = getenv("C2B_CPT") && atoi(getenv("C2B_CPT")) == 1;
-    const int cpt             = (!one_col && a.K >= 32) ? 2 : 1;
-    auto threads_for = [&](int ncol) {
-      int nt = ((ncol + cpt - 1) / cpt + 31) / 32 * 32;
-      return nt > kColThreads / cpt ? kColThreads / cpt : nt;
+    auto threads_for = [](int ncol) {
+      int nt = (ncol + 31) / 32 * 32;
+      return nt > kColThreads ? kColThreads : nt;
     };
     const unsigned grid = (unsigned)(a.batch * a.C);
     if (a.C > 1) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
       const int nt  = threads_for(JT + a.K);
-      const size_t smem = csweep_smem_doubles<JT>(nt * cpt < a.K ? nt * cpt : a.K) * sizeof(double);
-      if (cpt == 2)
-        C2B_LAUNCH("csweep_summary_kernel", stream, (csweep_tile_kernel<JT, LOWER, true, 2><<<grid, nt, smem, stream>>>(a)));
-      else
-        C2B_LAUNCH("csweep_summary_kernel", stream, (csweep_tile_kernel<JT, LOWER, true, 1><<<grid, nt, smem, stream>>>(a)));
+      const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
+      C2B_LAUNCH("csweep_summary_kernel", stream, (csweep_tile_kernel<JT, LOWER, true><<<grid, nt, smem, stream>>>(a)));
       int rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
     const int nt      = threads_for(a.K);
-    const size_t smem = csweep_smem_doubles<JT>(nt * cpt < a.K ? nt * cpt : a.K) * sizeof(double);
-    if (cpt == 2)
-      C2B_LAUNCH("csweep_apply_kernel", stream, (csweep_tile_kernel<JT, LOWER, false, 2><<<grid, nt, smem, stream>>>(a)));
-    else
-      C2B_LAUNCH("csweep_apply_kernel", stream, (csweep_tile_kernel<JT, LOWER, false, 1><<<grid, nt, smem, stream>>>(a)));
+    const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
+    C2B_LAUNCH("csweep_apply_kernel", stream, (csweep_tile_kernel<JT, LOWER, false><<<grid, nt, smem, stream>>>(a)));
   }
   return C2B_OK;
 }
