@@ -19,8 +19,8 @@ LIB = os.path.join(HERE, "libcelerite2_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 # (source, width or None).  The width lists must match C2B_DISPATCH_J_* in csrc/host_common.cuh.
-WIDTHS_SWEEP = [0, 1, 2, 3, 4, 5, 6, 7, 8, 16]
-WIDTHS_FACTOR = [0, 1, 2, 3, 4, 5, 6, 7, 8, 16]
+WIDTHS_SWEEP = list(range(0, 17))
+WIDTHS_FACTOR = list(range(0, 17))
 UNITS = (
     [("api_misc.cu", None), ("api_sweep.cu", None), ("api_factor.cu", None), ("api_noalloc.cu", None), ("api_predict.cu", None), ("api_terms.cu", None)]
     + [("inst_sweep.cu", w) for w in WIDTHS_SWEEP]

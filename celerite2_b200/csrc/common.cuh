@@ -27,7 +27,7 @@
 #define C2B_FREV_TILE 4  // rows per tile of the factor_rev apply pass (its tiles carry the J x J workspace rows)
 #endif
 
-// Compile-time width JT in 1..8 or 16 gives register arrays and fully unrolled loops; JT == 0 is the
+// Compile-time width JT in 1..16 gives register arrays and fully unrolled loops; JT == 0 is the
 // run-time-width fallback (J <= C2B_MAX_J, arrays live in local memory).
 template <int JT>
 struct Width {

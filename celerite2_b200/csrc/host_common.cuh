@@ -17,6 +17,13 @@ namespace c2b {
     case 6: CALL(6); break;                                                                                                               \
     case 7: CALL(7); break;                                                                                                               \
     case 8: CALL(8); break;                                                                                                               \
+    case 9: CALL(9); break;                                                                                                               \
+    case 10: CALL(10); break;                                                                                                             \
+    case 11: CALL(11); break;                                                                                                             \
+    case 12: CALL(12); break;                                                                                                             \
+    case 13: CALL(13); break;                                                                                                             \
+    case 14: CALL(14); break;                                                                                                             \
+    case 15: CALL(15); break;                                                                                                             \
     case 16: CALL(16); break;                                                                                                             \
     default: CALL(0); break;                                                                                                              \
   }

@@ -41,10 +41,12 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
     // workspace rows straight from registers (16-byte stores of each lane's column): r02b / r02e, -7 % on the factor
     // kernels against staging them in shared memory first; C2B_S_STAGED=1 keeps the staged form for A/B runs
     static const bool direct_s = getenv("C2B_S_STAGED") == nullptr;
-    // C2B_S_BULK=1: rows collected in shared memory and written by the TMA engine (bulk stores), see gfactor.cuh
-    static const bool bulk_s = getenv("C2B_S_BULK") != nullptr && atoi(getenv("C2B_S_BULK")) != 0;
+    // Chunked series: rows collected in shared memory and written by the TMA engine (bulk stores, gfactor.cuh); r02k:
+    // factor apply 0.121 -> 0.107 ms (c2), 1.55 -> 1.45 ms (c5).  Whole series per lane group (c3) are faster with the
+    // direct stores (5.70 vs 6.23 ms).  C2B_S_BULK=0 switches the bulk copies of factor and factor_rev off.
+    static const bool bulk_s = getenv("C2B_S_BULK") == nullptr || atoi(getenv("C2B_S_BULK")) != 0;
     if constexpr (JT % 2 == 0) {
-      if (bulk_s && g.S && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
+      if (bulk_s && g.C > 1 && g.S && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
         C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, false, true><<<grid, kGroupThreads, 0, stream>>>(g)));
         return C2B_OK;
       }
@@ -60,7 +62,7 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
 template <int JT>
 int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
   if (g.seg.phase != 0 && !(JT > 0 && JT <= 16)) {
-    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
   if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !no_group_kernels())) return launch_factor_group<JT>(g, sb, stream);
@@ -108,8 +110,8 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
       if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream))) return rc;
       g.carry = sb.states;
     }
-    // C2B_S_BULK=1: workspace rows of a tile by one bulk copy (gfactor_rev.cuh)
-    static const bool bulk_s = getenv("C2B_S_BULK") != nullptr && atoi(getenv("C2B_S_BULK")) != 0;
+    // workspace rows of a tile by one bulk copy (gfactor_rev.cuh); r02k: 0.156 -> 0.154 ms (c2), 2.49 -> 2.38 ms (c5)
+    static const bool bulk_s = getenv("C2B_S_BULK") == nullptr || atoi(getenv("C2B_S_BULK")) != 0;
     bool launched            = false;
     if constexpr (JT % 2 == 0) {
       if (bulk_s && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
@@ -129,7 +131,7 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
 template <int JT>
 int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   if (g.seg.phase != 0 && !(JT > 0 && JT <= 16)) {
-    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
   if (JT > 0 && JT <= 16 && (g.seg.phase != 0 || !no_group_kernels())) return launch_factor_rev_group<JT>(g, sb, bc, stream);

@@ -141,7 +141,7 @@ static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   if (a.seg.phase != 0 && !(JT > 0 && JT <= 16 && SOLVE && a.K == 1)) {
-    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 1..8, 16 only");
+    set_error("segments of a longer series: solve_lower / solve_upper with one right-hand side and J in 1..16 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
   if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !no_group_kernels()))
@@ -181,7 +181,7 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
 template <int JT, bool SOLVE, bool LOWER>
 int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStream_t stream) {
   if (a.seg.phase != 0 && !(JT > 0 && JT <= 16 && SOLVE && a.K == 1)) {
-    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 1..8, 16 only");
+    set_error("segments of a longer series: solve_lower_rev / solve_upper_rev with one right-hand side and J in 1..16 only");
     return C2B_ERR_INVALID_ARGUMENT;
   }
   if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !no_group_kernels()))

@@ -414,13 +414,14 @@ __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int
 
 
 // Which scan runs (measured on the B200, profiles/r02b_ab_runs.json, r02c_*):
-//   trees         (scan.cuh, round 1)  the default for one right-hand side: 64 us (AffV), 72 us (Cong), 128 us (Lft) at
-//                 C = 7,104, J = 6;
+//   trees         (scan.cuh, round 1)  64 us (AffV), 72 us (Cong), 128 us (Lft) at C = 7,104, J = 6; run when K > 1 and the
+//                 algebra is not affine (there is none today) or on request;
 //   blocked fold  (fold.cuh)           the default for the affine algebras with K > 1: the J x K state makes a tree
 //                 combine a warp-serial J x J x K product (c4: 255 us per sweep), a fold step is one CTA-parallel apply
 //                 (134 us per sweep).  At K = 1 its ~170 steps of ~0.6 us lose to the tree (102 us vs 64 us);
-//   prefix blocks (below)              2.7 % faster than the trees on the c2 step, but their in-place prefixes race between
-//                 column slices; kept as an A/B switch for K = 1 only.
+//   prefix blocks (below)              the default for one right-hand side: 2.5 % faster than the trees on the c2 step
+//                 (r02g, r02k: 0.971 -> 0.946 ms; full GPU suite green with them).  Their in-place prefixes race between
+//                 column slices, so they never run for K > 1.
 // C2B_SCAN (environment, read once) overrides: "tree", "prefix", "fold" (every affine scan), "fold+prefix".
 static inline const char *scan_mode() {
   static const char *v = [] {
@@ -429,12 +430,19 @@ static inline const char *scan_mode() {
   }();
   return v;
 }
-static inline bool scan_use_fold(int K) {
+// fold: every affine scan with K > 1; with one right-hand side the algebras that have the warp-level walks (fold.cuh:
+// AffV, compiled widths) once the series has enough chunks for two walks of sqrt(C) steps to beat a tree of 2 log2(C) levels
+constexpr int64_t kWfoldMinLeaves = 512;
+template <class Mon>
+static inline bool scan_use_fold(int K, int64_t leaves) {
   if (strstr(scan_mode(), "fold")) return true;
-  if (strstr(scan_mode(), "auto")) return K > 1;
+  if (strstr(scan_mode(), "auto")) return K > 1 || (Fold<Mon>::kWarp && leaves >= kWfoldMinLeaves);
   return false;
 }
-static inline bool scan_use_tree(int K) { return strstr(scan_mode(), "prefix") == nullptr || K > 1; }
+static inline bool scan_use_tree(int K) {
+  if (K > 1) return true;
+  return strstr(scan_mode(), "prefix") == nullptr && strstr(scan_mode(), "auto") == nullptr;
+}
 
 // Block size / warps / columns per slice of the prefix-block scan: the largest block whose shared memory (two element
 // buffers, the states, the warps' scratch) lets two CTAs share an SM, else one CTA per SM, narrower slices last.
@@ -536,7 +544,7 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   Levels lv          = make_levels(leaves);
   const int64_t nblk = (leaves + 31) / 32;
   if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
-    if (scan_use_fold(K)) {
+    if (scan_use_fold<Mon>(K, leaves)) {
       const Levels lvf = make_levels(leaves);
       double *heads    = nodes + (size_t)batch * lvf.total * Mon::esize(J, K);  // behind the nodes of all series (take_scan)
       return run_fold<Mon>(J, K, batch, leaves, lvf.total, nodes, states, heads, init, stream, mode);
@@ -620,7 +628,7 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
     return C2B_OK;
   } else {
   if (mode != 0) {
-    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
   const int threads  = 128;  // 4 warps
@@ -644,7 +652,7 @@ static inline int seg_export_root(int J, int K, int64_t leaves, const double *no
   const int es    = Mon::esize(J, K);
   int64_t root    = lv.off[lv.nlev - 1];
   if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
-    if (scan_use_fold(K)) {  // fold: the aggregate of the series sits behind the group aggregates
+    if (scan_use_fold<Mon>(K, leaves)) {  // fold: the aggregate of the series sits behind the group aggregates
       const FoldPlan fp = fold_plan<Mon>(J, K, leaves, lv.total);
       C2B_CUDA(cudaMemcpyAsync(summary_out, nodes + (fp.C + fp.ng) * es, sizeof(double) * es, cudaMemcpyDeviceToDevice, stream));
       return C2B_OK;
@@ -662,7 +670,7 @@ static inline int seg_export_root(int J, int K, int64_t leaves, const double *no
 template <class Mon>
 static inline int seg_import_state(int J, int K, int64_t leaves, double *states, const double *state_in, cudaStream_t stream) {
   if constexpr (Mon::kCoop && Fold<Mon>::kAffine) {
-    if (scan_use_fold(K)) return C2B_OK;  // the fold takes the entering state through run_scan's `init`
+    if (scan_use_fold<Mon>(K, leaves)) return C2B_OK;  // the fold takes the entering state through run_scan's `init`
   }
   if constexpr (Mon::kCoop) {
     if (!scan_use_tree(K)) return C2B_OK;  // prefix blocks take the entering state through run_scan's `init`
@@ -709,7 +717,7 @@ static inline int run_seg_carry(int J, int K, int nseg, int which, bool descendi
     C2B_LAUNCH("seg_carry_kernel", stream, (seg_carry_kernel<Mon><<<1, 32, smem, stream>>>(J, K, nseg, which, descending, summaries, out)));
     return C2B_OK;
   } else {
-    set_error("segments of a longer series need a compiled width (J in 1..8, 16)");
+    set_error("segments of a longer series need a compiled width (J in 1..16)");
     return C2B_ERR_INVALID_ARGUMENT;
   }
 }

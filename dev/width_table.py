@@ -1,5 +1,5 @@
-"""Per-width timing table: ms per operator at N = 1e6, K = 1 for every compiled width J = 1..8, 16 and
-one run-time width (J = 9) for comparison.  Kernels: J real terms / SHO terms as needed.  Output: gpurun_out/r02_width_table.json"""
+"""Per-width timing table: ms per operator at N = 1e6, K = 1 for every compiled width J = 1..16 and
+one run-time width (J = 17) for comparison.  Kernels: J real terms / SHO terms as needed.  Output: gpurun_out/r02_width_table.json"""
 import json, os, sys
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
 import numpy as np, torch
@@ -27,7 +27,7 @@ def timeit(fn, steps=10, warm=3):
     return e0.elapsed_time(e1) / steps
 
 out = {}
-for J in (1, 2, 3, 4, 5, 6, 7, 8, 9, 16):
+for J in tuple(range(1, 18)):
     co = [T(v) for v in kernel(J)]
     c, a, U, V = ops.get_celerite_matrices(*co, t, diag)
     d, W, S, st = ops.factor(t, c, a, U, V)
@@ -49,5 +49,5 @@ for J in (1, 2, 3, 4, 5, 6, 7, 8, 9, 16):
     print(J, out["J=%d" % J], flush=True)
     del c, a, U, V, d, W, S, Z, F, bt, bc, bU, bW, bY
     torch.cuda.empty_cache()
-json.dump({"_what": "ms per operator call, N = 1e6, K = 1, one B200, CUDA events, 10 timed calls after 3 warm-up calls; J = 9 takes the run-time-width path", "rows": out},
+json.dump({"_what": "ms per operator call, N = 1e6, K = 1, one B200, CUDA events, 10 timed calls after 3 warm-up calls; J = 17 takes the run-time-width path", "rows": out},
           open(os.path.join(os.path.dirname(__file__), "..", "gpurun_out", "r02_width_table.json"), "w"), indent=1)

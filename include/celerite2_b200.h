@@ -18,7 +18,7 @@
  *   - return value: 0 on success, a negative C2B_ERR_* code otherwise (text via c2b_last_error()).
  *     Nothing here synchronises the device; numerical failure of `factor` is reported through the
  *     device-side `status` array, exactly one int64 per series (see c2b_factor).
- *   - supported widths: 1 <= J <= 32 (compiled fast paths for J = 1..8 and 16), any K >= 1, any N >= 1.
+ *   - supported widths: 1 <= J <= 32 (compiled fast paths for J = 1..16), any K >= 1, any N >= 1.
  */
 #ifndef CELERITE2_B200_H_
 #define CELERITE2_B200_H_
@@ -167,7 +167,7 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
  * run of rows [r0, r1) of the series; the caller passes pointers to the segment's first row (t + r0, U + r0*J, ...) and
  * N = r1 - r0.  The time stamps of the neighbouring rows must be addressable through the same pointer when has_left /
  * has_right say so (t[-1], t[N]): replicate t on every device or keep a one-element halo.  batch must be 1 and the
- * width one of the compiled ones (J in 1..8, 16; sweeps: K = 1).  Each of the four operators of the
+ * width one of the compiled ones (J in 1..16; sweeps: K = 1).  Each of the four operators of the
  * log-likelihood + gradient pipeline runs in two calls with the SAME scratch buffer (which holds the tree in between):
  *   phase C2B_SEG_SUMMARISE: summary pass + up-sweep; the segment's summary element (c2b_segment_sizes doubles) is
  *                            written to summary_out.  Exchange the summaries of all segments (all-gather),

@@ -23,12 +23,33 @@ def _case(seed):
 
 @pytest.mark.parametrize("seed", range(42))
 def test_fuzz_all_operators(seed):
+    name, N, K, chunks, batch = _case(seed)
+    _check(ALL_KERNELS[name], name, N, K, chunks, batch, seed)
+
+
+def _width_kernel(J):
+    """J columns: SHO terms (two columns each) plus one real term when J is odd."""
+    from celerite2_b200 import workloads as wl
+
+    terms = [wl.sho_coeffs(1.0 / (i + 1), 0.5 + 0.7 * i, 1.0 + 0.5 * i) for i in range(J // 2)]
+    if J % 2:
+        terms.append(wl.real_coeffs(0.7, 0.3))
+    return wl.sum_coeffs(*terms)
+
+
+@pytest.mark.parametrize("J", list(range(1, 18)))
+def test_every_width_all_operators(J):
+    """Every compiled width (1..16) and one run-time width (17), one and three right-hand sides, whole series and chunks."""
+    for K, chunks in ((1, 0), (1, 6), (3, 6)):
+        _check(_width_kernel(J), "J=%d" % J, 333 + 7 * J, K, chunks, 1, 100 + J)
+
+
+def _check(coeffs, name, N, K, chunks, batch, seed):
     import torch
 
     import oracle
     from celerite2_b200 import ops
 
-    name, N, K, chunks, batch = _case(seed)
     P = oracle.port()
     dev = torch.device("cuda:0")
     T = lambda x: torch.as_tensor(np.ascontiguousarray(x, dtype=np.float64), device=dev)
@@ -37,7 +58,7 @@ def test_fuzz_all_operators(seed):
     ts = [np.sort(rng.uniform(0, 0.1 * max(N, 2), N)) + 1e-3 * np.arange(N) for _ in range(batch)]
     diags = [rng.uniform(0.1, 0.3, N) ** 2 for _ in range(batch)]
     Ys = [rng.standard_normal((N, K)) for _ in range(batch)]
-    mats = [P.get_celerite_matrices(*ALL_KERNELS[name], t, dg) for t, dg in zip(ts, diags)]
+    mats = [P.get_celerite_matrices(*coeffs, t, dg) for t, dg in zip(ts, diags)]
     c = mats[0][0]
     J = mats[0][2].shape[1]
     st = lambda xs: T(np.stack(xs)) if batch > 1 else T(xs[0])

@@ -181,8 +181,17 @@ def test_split_series_full_size_against_reference(env, nseg):
     for nm, want in (("d", pipe.d), ("W", pipe.W), ("Z", pipe.Z), ("bV", pipe.bV), ("ba", pipe.ba), ("bU", pipe.bU + pipe.bU2), ("bY", pipe.bY)):
         got = np.concatenate([H(getattr(s, nm)).reshape((s.n,) + want.shape[1:]) for s in segs])
         worst[nm] = relerr(got, want)
-    bad = {k: v for k, v in worst.items() if not v < TOL}
-    assert not bad, "split into %d: arrays over 1e-10: %r (all: %r)" % (nseg, bad, worst)
+    # grad_dc is the one ill-conditioned number of the evaluation: a sum over all rows of t_n-weighted terms of both signs.
+    # Element-wise relative noise of 3e-11 on bU and bV (what two builds of the REFERENCE differ by on these arrays) moves
+    # it by 5e-8 .. 2e-7; its bar is 1e-9, every other output keeps 1e-10.  Measured: 9e-12 .. 1.7e-10 depending on where
+    # the chunk boundaries fall (the un-split evaluation shows the same spread when its chunk length changes).
+    rng = np.random.default_rng(5)
+    noisy = oracle.get_celerite_matrices_rev(*cfg["coeffs"], t, bc, pipe.ba, (pipe.bU + pipe.bU2) * (1 + 3e-11 * rng.standard_normal(pipe.bU.shape)),
+                                             pipe.bV * (1 + 3e-11 * rng.standard_normal(pipe.bV.shape)))
+    assert relerr(noisy[5], g[5]) > 1e-8, "grad_dc is expected to be ill-conditioned on this workload"
+    bars = {"grad_dc": 1e-9}
+    bad = {k: v for k, v in worst.items() if not v < bars.get(k, TOL)}
+    assert not bad, "split into %d: arrays over their bars: %r (all: %r)" % (nseg, bad, worst)
 
 
 # ---- adjoint of the assembly against its restatement ----------------------------------------------------------------

@@ -71,7 +71,7 @@ def test_segment_argument_errors():
 
     lib = _lib.lib
     dev = torch.device("cuda:0")
-    x = torch.zeros(64 * 9, dtype=torch.float64, device=dev)
+    x = torch.zeros(64 * 17, dtype=torch.float64, device=dev)
     st = torch.zeros(1, dtype=torch.int64, device=dev)
     seg = _lib.Segment(_lib.SEG_SUMMARISE, 0, 0, 0, None, x.data_ptr(), None)
     p = x.data_ptr()
@@ -80,7 +80,7 @@ def test_segment_argument_errors():
     assert rc != 0 and b"scratch" in lib.c2b_last_error()
     # a width without compiled lane-group kernels: refused
     buf = torch.empty(1 << 20, dtype=torch.uint8, device=dev)
-    rc = lib.c2b_factor_segment(64, 9, 1, p, p, p, p, p, p, p, None, st.data_ptr(), 3, buf.data_ptr(), buf.numel(), None, ctypes.byref(seg))
+    rc = lib.c2b_factor_segment(64, 17, 1, p, p, p, p, p, p, p, None, st.data_ptr(), 3, buf.data_ptr(), buf.numel(), None, ctypes.byref(seg))
     assert rc != 0 and b"compiled width" in lib.c2b_last_error()
     e, s = ctypes.c_int64(), ctypes.c_int64()
     assert lib.c2b_segment_sizes(_lib.OP_IDS["factor"], 6, 1, ctypes.byref(e), ctypes.byref(s)) == 0 and (e.value, s.value) == (108, 36)
