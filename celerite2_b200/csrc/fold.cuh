@@ -29,14 +29,12 @@ constexpr int kFoldMaxThreads = 512;
 template <class Mon>
 struct Fold {
   static constexpr bool kAffine = false;
-  static constexpr bool kWarp   = false;  // has the warp-level walks for one right-hand side (wfold_* below)
 };
 
 // ---- AffV: s -> M s + b, head M (J x J row-major), state J x K (index j + J k) ------------------------------------------
 template <int JT>
 struct Fold<AffV<JT>> {
   static constexpr bool kAffine = true;
-  static constexpr bool kWarp   = JT > 0;
   __host__ __device__ static int hsize(int J) { return J * J; }
   __host__ __device__ static int scratch(int, int) { return 0; }
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
@@ -83,7 +81,6 @@ struct Fold<AffV<JT>> {
 template <int JT>
 struct Fold<DiagV<JT>> {
   static constexpr bool kAffine = true;
-  static constexpr bool kWarp   = false;
   __host__ __device__ static int hsize(int J) { return J; }
   __host__ __device__ static int scratch(int, int) { return 0; }
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
@@ -105,7 +102,6 @@ struct Fold<DiagV<JT>> {
 template <int JT>
 struct Fold<Cong<JT>> {
   static constexpr bool kAffine = true;
-  static constexpr bool kWarp   = false;
   __host__ __device__ static int hsize(int J) { return J * J; }
   __host__ __device__ static int scratch(int J, int) { return 2 * J * J; }
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
@@ -354,141 +350,6 @@ __global__ void __launch_bounds__(256) fold_finish_kernel(int J_, int K, FoldPla
     for (int o = tid; o < ss; o += nt) states[i * ssg + (o < sh ? o : o - sh + sgo)] = out[o];
 }
 
-// =================================================================================================================
-// One right-hand side, compile-time width, AffV: the two sequential walks by ONE WARP each, without a barrier or a
-// cross-lane exchange per step.  The CTA-wide kernels above spend ~0.6 us per step at K = 1 (r02p: ~200 instructions
-// around a handful of multiply-adds), which made the fold lose to the trees (102 us vs 64 us per scan of 7,104 chunks).
-// Here lane c < J owns column c of the head product H, lane J the state: every lane pushes ITS vector through the
-// element, v <- M v (+ b for the state), M read from shared memory as broadcasts: J x J multiply-adds in J independent
-// chains, nothing else.  Elements arrive through a per-warp cp.async ring, kWfoldDepth ahead of the walk.
-// =================================================================================================================
-constexpr int kWfoldDepth = 8;
-// groups (warps) per CTA in phase A: as many as keep the rings under the 48 KB of static shared memory
-template <int J>
-struct WfoldWarps {
-  static constexpr int value = (4 * kWfoldDepth * (J * J + J) * 8 <= 48 * 1024) ? 4 : 2;
-};
-
-template <int J>
-C2B_DEV void wfold_mv(const double *e, double *v, bool add_b) {
-  double out[J];
-#pragma unroll
-  for (int r = 0; r < J; ++r) {
-    double s = add_b ? e[J * J + r] : 0.0;
-#pragma unroll
-    for (int j = 0; j < J; ++j) s = fma(e[r * J + j], v[j], s);
-    out[r] = s;
-  }
-#pragma unroll
-  for (int r = 0; r < J; ++r) v[r] = out[r];
-}
-
-// element i of `src` (ES doubles each, ES even, 16-byte aligned) -> ring slot i mod depth
-template <int ES>
-C2B_DEV void wfold_fetch(double *ring, const double *src, int i, int lane) {
-  double *dst = ring + (i % kWfoldDepth) * ES;
-#pragma unroll
-  for (int q0 = 0; q0 < ES; q0 += 64) {
-    const int q = q0 + 2 * lane;
-    if (q < ES) cp_async16(dst + q, src + q);
-  }
-}
-
-// phase A: one warp per group
-template <int J>
-__global__ void __launch_bounds__(32 * WfoldWarps<J>::value) wfold_groups_kernel(FoldPlan fp, int64_t batch, double *nodes_all, double *states_all,
-                                                                        double *heads_all) {
-  constexpr int ES = J * J + J, HS = J * J, kWfoldWarps = WfoldWarps<J>::value;
-  __shared__ __align__(16) double ring[kWfoldWarps][kWfoldDepth * ES];
-  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const int64_t unit = (int64_t)blockIdx.x * kWfoldWarps + w;
-  if (unit >= batch * fp.ng) return;  // (no CTA-wide barriers below)
-  const int64_t b = unit / fp.ng, g = unit % fp.ng;
-  const int64_t first = g * fp.B;
-  const int cnt       = (int)(fp.C - first < fp.B ? fp.C - first : fp.B);
-  double *nodes = nodes_all + b * fp.stride * ES, *states = states_all + b * fp.stride * J;
-  double *heads = heads_all + (b * fp.C + first) * (int64_t)HS;
-  double *rb    = ring[w];
-  auto issue = [&](int i) {
-    if (i < cnt) wfold_fetch<ES>(rb, nodes + (first + i) * ES, i, lane);
-    cp_async_commit();
-  };
-  for (int i = 0; i < kWfoldDepth; ++i) issue(i);
-  double v[J];
-#pragma unroll
-  for (int r = 0; r < J; ++r) v[r] = (r == lane) ? 1.0 : 0.0;  // lanes >= J: zero (lane J is the state, from zero)
-  for (int i = 0; i < cnt; ++i) {
-    cp_async_wait<kWfoldDepth - 1>();
-    __syncwarp();
-    const double *e = rb + (i % kWfoldDepth) * ES;
-    // what enters chunk i when the group starts from zero, and the head product of the chunks before it
-    if (lane < J) {
-#pragma unroll
-      for (int r = 0; r < J; ++r) heads[(int64_t)i * HS + r * J + lane] = v[r];
-    } else if (lane == J) {
-#pragma unroll
-      for (int r = 0; r < J; ++r) states[(first + i) * J + r] = v[r];
-    }
-    if (lane <= J) wfold_mv<J>(e, v, lane == J);
-    __syncwarp();  // the slot is free
-    issue(i + kWfoldDepth);
-  }
-  double *agg = nodes + (fp.C + g) * ES;  // [head product | state reached from zero]
-  if (lane < J) {
-#pragma unroll
-    for (int r = 0; r < J; ++r) agg[r * J + lane] = v[r];
-  } else if (lane == J) {
-#pragma unroll
-    for (int r = 0; r < J; ++r) agg[HS + r] = v[r];
-  }
-}
-
-// phase B: one warp per series over the group aggregates.  Lane J: the states entering the groups, from `init` (NULL =
-// zero), when want_states.  Lanes < J and lane J + 1: head product and state from zero = the aggregate of the series, when
-// want_root.
-template <int J>
-__global__ void __launch_bounds__(32) wfold_top_kernel(FoldPlan fp, bool want_states, bool want_root, double *nodes_all, double *states_all,
-                                                       const double *init) {
-  constexpr int ES = J * J + J, HS = J * J;
-  static_assert(J + 2 <= 32, "head columns, the state and the state from zero share a warp");
-  __shared__ __align__(16) double rb[kWfoldDepth * ES];
-  const int lane  = threadIdx.x;
-  const int64_t b = blockIdx.x;
-  double *nodes = nodes_all + b * fp.stride * ES, *states = states_all + b * fp.stride * J;
-  const int n = (int)fp.ng;
-  auto issue = [&](int g) {
-    if (g < n) wfold_fetch<ES>(rb, nodes + (fp.C + g) * ES, g, lane);
-    cp_async_commit();
-  };
-  for (int g = 0; g < kWfoldDepth; ++g) issue(g);
-  double v[J];
-#pragma unroll
-  for (int r = 0; r < J; ++r) v[r] = (r == lane) ? 1.0 : ((lane == J && init) ? init[b * J + r] : 0.0);
-  const bool active = lane < J ? want_root : (lane == J ? want_states : (lane == J + 1 ? want_root : false));
-  for (int g = 0; g < n; ++g) {
-    cp_async_wait<kWfoldDepth - 1>();
-    __syncwarp();
-    const double *e = rb + (g % kWfoldDepth) * ES;
-    if (want_states && lane == J) {
-#pragma unroll
-      for (int r = 0; r < J; ++r) states[(fp.C + g) * J + r] = v[r];
-    }
-    if (active) wfold_mv<J>(e, v, lane >= J);
-    __syncwarp();
-    issue(g + kWfoldDepth);
-  }
-  if (want_root) {
-    double *root = nodes + (fp.C + fp.ng) * ES;
-    if (lane < J) {
-#pragma unroll
-      for (int r = 0; r < J; ++r) root[r * J + lane] = v[r];
-    } else if (lane == J + 1) {
-#pragma unroll
-      for (int r = 0; r < J; ++r) root[HS + r] = v[r];
-    }
-  }
-}
-
 template <class Mon>
 static inline FoldPlan fold_plan(int J, int K, int64_t leaves, int64_t stride) {
   using F = Fold<Mon>;
@@ -536,23 +397,6 @@ static inline int run_fold(int J, int K, int64_t batch, int64_t leaves, int64_t 
   if (fp.smemC > 48 * 1024)
     C2B_CUDA(cudaFuncSetAttribute(fold_finish_kernel<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fp.smemC));
   const unsigned ns = (unsigned)fp.nslices;
-  if constexpr (Fold<Mon>::kWarp) {
-    if (K == 1) {
-      constexpr int JT = Mon::kJT, kWfoldWarps = WfoldWarps<JT>::value;
-      if (mode != 2)
-        C2B_LAUNCH("wfold_groups_kernel", stream,
-                   (wfold_groups_kernel<JT><<<(unsigned)((batch * fp.ng + kWfoldWarps - 1) / kWfoldWarps), 32 * kWfoldWarps, 0, stream>>>(
-                       fp, batch, nodes, states, heads)));
-      C2B_LAUNCH("wfold_top_kernel", stream, (wfold_top_kernel<JT><<<(unsigned)batch, 32, 0, stream>>>(fp, mode != 1, mode == 1, nodes, states, init)));
-      if (mode != 1) {
-        const int cpb     = 256 / fp.fthreads;
-        const int64_t per = (fp.C + cpb - 1) / cpb;
-        C2B_LAUNCH("fold_finish_kernel", stream,
-                   (fold_finish_kernel<Mon><<<dim3((unsigned)(batch * per), 1), 256, fp.smemC, stream>>>(J, K, fp, states, heads)));
-      }
-      return C2B_OK;
-    }
-  }
   if (mode != 2)
     C2B_LAUNCH("fold_groups_kernel", stream,
                (fold_groups_kernel<Mon><<<dim3((unsigned)(batch * fp.ng), ns), fp.threads, fp.smemA, stream>>>(J, K, fp, nodes, states, heads)));

@@ -430,13 +430,13 @@ static inline const char *scan_mode() {
   }();
   return v;
 }
-// fold: every affine scan with K > 1; with one right-hand side the algebras that have the warp-level walks (fold.cuh:
-// AffV, compiled widths) once the series has enough chunks for two walks of sqrt(C) steps to beat a tree of 2 log2(C) levels
-constexpr int64_t kWfoldMinLeaves = 512;
+// fold: every affine scan with K > 1.  With one right-hand side both fold variants lost to the prefix blocks on the c2
+// step: CTA-wide walks 102 us per scan (r02c), one-warp walks without barriers 71 us (r02n, commit 33fd0f1: a lone warp
+// issues one instruction per ~6 cycles, 139 instructions per step), prefix blocks 52 us.
 template <class Mon>
-static inline bool scan_use_fold(int K, int64_t leaves) {
+static inline bool scan_use_fold(int K, int64_t) {
   if (strstr(scan_mode(), "fold")) return true;
-  if (strstr(scan_mode(), "auto")) return K > 1 || (Fold<Mon>::kWarp && leaves >= kWfoldMinLeaves);
+  if (strstr(scan_mode(), "auto")) return K > 1;
   return false;
 }
 static inline bool scan_use_tree(int K) {
