@@ -144,6 +144,9 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm, i
     if (units > 0) target = units;
     const int64_t have = batch * (cols > 0 ? cols : 1);
     C                  = have >= target ? 1 : target / have;
+    // chunking doubles the passes over the rows (summary + apply): two chunks per series buy nothing in the latency-bound
+    // regime (half the rows per lane group, twice the passes; r02r: c3 30.4 -> 35.6 ms when its 8,192 series were cut in two)
+    if (C == 2) C = 1;
     if (C > 16384 && units <= 0) C = 16384;
     // shortest chunk worth a summary pass; short series are latency-bound (one warp walks a chunk row by row), so they
     // are cut finer (c1: N = 1000)

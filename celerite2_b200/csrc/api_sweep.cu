@@ -3,9 +3,22 @@
 
 namespace c2b {
 
+// CTAs per SM the chunk plan of a K = 1 sweep is sized for: what the kernels of the width can really keep resident (the
+// launch bounds only promise C2B_MINB_SWEEP; at J = 6 the registers and tiles allow 8, r02e: summary and apply passes
+// -10 % with 8 resident CTAs), never more than 8 (more chunks cost the scans more than the passes gain)
+static int sweep_ctas(int J, int K) {
+  if (K != 1) return C2B_MINB_SWEEP;
+  int occ = 0;
+#define CALL(JT) occ = sweep_resident_ctas<JT>()
+  C2B_DISPATCH_J_SWEEP(J, CALL)
+#undef CALL
+  if (occ < C2B_MINB_SWEEP) return C2B_MINB_SWEEP;
+  return occ > 8 ? 8 : occ;
+}
+
 static int sizes_sweep(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb) {
   static const int64_t units = env_units("C2B_UNITS_SWEEP");
-  *pl = make_plan(N, batch, (K + 7) / 8, J, C2B_MINB_SWEEP, K == 1 ? units : 0);  // K columns already supply parallelism: fewer chunks per series
+  *pl = make_plan(N, batch, (K + 7) / 8, J, sweep_ctas(J, K), K == 1 ? units : 0);  // K columns already supply parallelism: fewer chunks per series
   if (pl->C > 1 || batch == 1) {
     const int es = solve ? J * J + J * K : J + J * K;
     take_scan(ar, batch, pl->C, es, J * K, sb);
@@ -24,7 +37,7 @@ size_t scratch_sweep(bool solve, int64_t N, int J, int K, int64_t batch) {
 static int sizes_sweep_rev(bool solve, int64_t N, int J, int K, int64_t batch, Plan *pl, Arena &ar, ScanBuffers *sb, double **bc_part,
                            double **bt_edge) {
   static const int64_t units = env_units("C2B_UNITS_SWEEP");
-  *pl = make_plan(N, batch, (K + 7) / 8, J, C2B_MINB_SWEEP, K == 1 ? units : 0);  // K columns already supply parallelism: fewer chunks per series
+  *pl = make_plan(N, batch, (K + 7) / 8, J, sweep_ctas(J, K), K == 1 ? units : 0);  // K columns already supply parallelism: fewer chunks per series
   if (pl->C > 1 || batch == 1) {
     const int es = solve ? J * J + J * K : J + J * K;
     take_scan(ar, batch, pl->C, es, J * K, sb);

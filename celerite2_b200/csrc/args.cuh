@@ -102,5 +102,9 @@ template <int JT>
 int launch_seg_carry_factor(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream);
 template <int JT>
 int launch_seg_carry_sweep(int kind, int nseg, int which, const double *summaries, double *out, cudaStream_t stream);
+// CTAs per SM that the four K = 1 lane-group kernels of a solve (summary, apply, and their reverse-mode pair) can all keep
+// resident, from the occupancy calculator (registers and shared memory as compiled); 0 for a run-time width (inst_sweep.cu)
+template <int JT>
+int sweep_resident_ctas();
 
 }  // namespace c2b

@@ -249,6 +249,29 @@ int launch_seg_carry_sweep(int kind, int nseg, int which, const double *summarie
   return run_seg_carry<AffV<JT>>(JT, 1, nseg, which, kind == 3 || kind == 4, summaries, out, stream);
 }
 
+template <int JT>
+int sweep_resident_ctas() {
+  if constexpr (JT > 0 && JT <= 16) {
+    static int cached[64] = {0};
+    int dev               = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+    if (cached[dev] == 0) {
+      int a = 0, b = 0, c = 0, d = 0;
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, gsweep_summary_kernel<JT, true>, kGroupThreadsS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, gsweep_apply_kernel<JT, true, true>, kGroupThreadsS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c, gsweep_rev_summary_kernel<JT, true>, kGroupThreadsS, 0);
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d, gsweep_rev_apply_kernel<JT, true, true>, kGroupThreadsS, 0);
+      int m = a < b ? a : b;
+      m     = m < c ? m : c;
+      m     = m < d ? m : d;
+      cached[dev] = m > 0 ? m : -1;
+    }
+    return cached[dev] > 0 ? cached[dev] : 0;
+  } else {
+    return 0;
+  }
+}
+template int sweep_resident_ctas<C2B_JT>();
 template int launch_seg_carry_sweep<C2B_JT>(int, int, int, const double *, double *, cudaStream_t);
 
 #define INST(S, L)                                                                                                                        \
