@@ -107,6 +107,12 @@ static int sm_count() {
 
 // Developer switch, read from the environment once per process: C2B_NO_GROUP=1 routes the compiled widths to the
 // generic thread-per-chunk kernels (A/B comparisons on the GPU box).  Not part of the ABI.
+// C2B_PDL: 0 no programmatic dependent launches, 1 (default) the ops of a chunked batch, 2 every launch (common.cuh)
+int pdl_mode() {
+  static const int v = getenv("C2B_PDL") ? atoi(getenv("C2B_PDL")) : 1;
+  return v;
+}
+thread_local bool g_pdl_wave = false;
 bool no_group_kernels() {
   static const bool v = getenv("C2B_NO_GROUP") != nullptr;
   return v;
@@ -171,6 +177,7 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm, i
   pl.L = (N + C - 1) / C;
   if (C > 1 && (pl.L & 1)) pl.L += 1;  // even chunk starts keep the 8-byte-per-row arrays 16-byte aligned for bulk copies
   pl.C = (N + pl.L - 1) / pl.L;
+  g_pdl_wave = batch > 1 && pl.C > 1;  // (the plan of the op about to be launched on this thread)
   return pl;
 }
 
@@ -263,15 +270,15 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
   } else if (pl.C > 1) {
     g.leaves      = sb.nodes;
     g.node_stride = sb.node_stride;
-    C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, true><<<grid, block, 0, stream>>>(g));
+    C2B_LAUNCH("gm_scan_kernel", stream, launch_k(gm_scan_kernel<UPPER, true>, grid, block, 0, stream, g));
     rc = run_scan<DiagV<0>>(J, K, 1, pl.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
-  if (!states_done) C2B_LAUNCH("gm_scan_kernel", stream, gm_scan_kernel<UPPER, false><<<grid, block, 0, stream>>>(g));
-  C2B_LAUNCH("gm_gather_kernel", stream, gm_gather_kernel<UPPER><<<(unsigned)((N * K + 127) / 128), 128, 0, stream>>>(g));
+  if (!states_done) C2B_LAUNCH("gm_scan_kernel", stream, launch_k(gm_scan_kernel<UPPER, false>, grid, block, 0, stream, g));
+  C2B_LAUNCH("gm_gather_kernel", stream, launch_k(gm_gather_kernel<UPPER>, (unsigned)((N * K + 127) / 128), 128, 0, stream, g));
   if (F) {
-    C2B_LAUNCH("gm_workspace_kernel", stream, gm_workspace_kernel<UPPER><<<(unsigned)((M * (int64_t)J * K + 127) / 128), 128, 0, stream>>>(g));
+    C2B_LAUNCH("gm_workspace_kernel", stream, launch_k(gm_workspace_kernel<UPPER>, (unsigned)((M * (int64_t)J * K + 127) / 128), 128, 0, stream, g));
   }
   return C2B_OK;
 }
@@ -280,6 +287,7 @@ static int general_matmul_entry(int64_t N, int64_t M, int J, int K, const double
 // K(n,m) = K(m,n) = sum_j U(n,j) V(m,j) exp(-c_j (t_n - t_m)) for n > m.  One thread per element of the lower triangle.
 static __global__ void __launch_bounds__(256) to_dense_kernel(int64_t N, int J, const double *t, const double *c, const double *a,
                                                               const double *U, const double *V, double *K) {
+  pdl_prologue();
   const int64_t total = N * N;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t n = i / N, m = i - n * N;
@@ -309,7 +317,7 @@ int c2b_to_dense(int64_t N, int32_t J, const double *t, const double *c, const d
   C2B_REQUIRE(t && c && a && U && V && K_out, "null data pointer");
   int64_t blocks = (N * N + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
-  C2B_LAUNCH("to_dense_kernel", (cudaStream_t)stream, (to_dense_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(N, J, t, c, a, U, V, K_out)));
+  C2B_LAUNCH("to_dense_kernel", (cudaStream_t)stream, (launch_k(to_dense_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, N, J, t, c, a, U, V, K_out)));
   return C2B_OK;
 }
 
@@ -405,7 +413,7 @@ int c2b_get_celerite_matrices(int32_t layout, int64_t N, int32_t Jr, int32_t Jc,
   const size_t smem = (size_t)2 * kAsmThreads * (Jr + 2 * Jc) * sizeof(double);
   if (smem > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
   C2B_LAUNCH("assemble_kernel", (cudaStream_t)stream_,
-             assemble_kernel<<<(unsigned)((total + kAsmThreads - 1) / kAsmThreads), kAsmThreads, smem, (cudaStream_t)stream_>>>(g));
+             launch_k(assemble_kernel, (unsigned)((total + kAsmThreads - 1) / kAsmThreads), kAsmThreads, smem, (cudaStream_t)stream_, g));
   return C2B_OK;
 }
 
@@ -442,8 +450,8 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
   g.ctas_per_series = asm_rev_ctas(N);
   const int nred    = Jr + 3 * Jc;
   dim3 grid((unsigned)g.ctas_per_series, (unsigned)batch);
-  C2B_LAUNCH("assemble_rev_kernel", stream, assemble_rev_kernel<<<grid, kAsmRevThreads, (size_t)nred * kAsmRevThreads * sizeof(double), stream>>>(g));
-  C2B_LAUNCH("assemble_rev_final_kernel", stream, assemble_rev_final_kernel<<<(unsigned)batch, 256, 0, stream>>>(g));
+  C2B_LAUNCH("assemble_rev_kernel", stream, launch_k(assemble_rev_kernel, grid, kAsmRevThreads, (size_t)nred * kAsmRevThreads * sizeof(double), stream, g));
+  C2B_LAUNCH("assemble_rev_final_kernel", stream, launch_k(assemble_rev_final_kernel, (unsigned)batch, 256, 0, stream, g));
   return C2B_OK;
 }
 
@@ -460,8 +468,8 @@ int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, 
   if (rc) return rc;
   const int ctas = red_ctas(N);
   dim3 grid((unsigned)ctas, (unsigned)batch);
-  C2B_LAUNCH("norm_logdet_kernel", stream, norm_logdet_kernel<<<grid, kRedThreads, 0, stream>>>(N, d, z, bz, bd, (double *)sc.ptr, ctas));
-  C2B_LAUNCH("norm_logdet_final_kernel", stream, norm_logdet_final_kernel<<<(unsigned)batch, 64, 0, stream>>>((const double *)sc.ptr, ctas, out));
+  C2B_LAUNCH("norm_logdet_kernel", stream, launch_k(norm_logdet_kernel, grid, kRedThreads, 0, stream, N, d, z, bz, bd, (double *)sc.ptr, ctas));
+  C2B_LAUNCH("norm_logdet_final_kernel", stream, launch_k(norm_logdet_final_kernel, (unsigned)batch, 64, 0, stream, (const double *)sc.ptr, ctas, out));
   return C2B_OK;
 }
 
@@ -472,7 +480,7 @@ int c2b_add_inplace(int64_t n, const double *x, double *y, void *stream_) {
   if (n == 0) return C2B_OK;
   int64_t blocks = (n + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  C2B_LAUNCH("add_inplace_kernel", (cudaStream_t)stream_, add_inplace_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream_>>>(n, x, y));
+  C2B_LAUNCH("add_inplace_kernel", (cudaStream_t)stream_, launch_k(add_inplace_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream_, n, x, y));
   return C2B_OK;
 }
 

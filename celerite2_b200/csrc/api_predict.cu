@@ -50,6 +50,7 @@ C2B_DEV void load_coeffs(KernelCoeffs *dst, int Jr, int Jc, const double *ar, co
 static __global__ void __launch_bounds__(256) kernel_matrix_kernel(int64_t N, int64_t M, int Jr, int Jc, const double *ar, const double *cr,
                                                                    const double *ac, const double *bc, const double *cc, const double *dc,
                                                                    const double *x1, const double *x2, double *out) {
+  pdl_prologue();
   __shared__ KernelCoeffs k;
   load_coeffs(&k, Jr, Jc, ar, cr, ac, bc, cc, dc);
   const int64_t total = N * M;
@@ -66,6 +67,7 @@ static __global__ void __launch_bounds__(32 * kVarRows) variance_partial_kernel(
                                                                               const double *bc, const double *cc, const double *dc,
                                                                               const double *x1, const double *x2, const double *Z,
                                                                               double *part) {
+  pdl_prologue();
   __shared__ KernelCoeffs k;
   __shared__ double red[kVarRows][33];
   load_coeffs(&k, Jr, Jc, ar, cr, ac, bc, cc, dc);
@@ -90,6 +92,7 @@ static __global__ void __launch_bounds__(32 * kVarRows) variance_partial_kernel(
 
 static __global__ void __launch_bounds__(256) variance_final_kernel(int64_t M, int64_t nchunk, int Jr, int Jc, const double *ar,
                                                                     const double *ac, const double *part, double *var) {
+  pdl_prologue();
   const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= M) return;
   double k0 = 0.0;  // k(0) = sum ar + sum ac
@@ -133,7 +136,7 @@ int c2b_kernel_matrix(int64_t N, int64_t M, int32_t Jr, int32_t Jc, const double
   int64_t blocks = (N * M + 255) / 256;
   if (blocks > 148 * 32) blocks = 148 * 32;
   C2B_LAUNCH("kernel_matrix_kernel", (cudaStream_t)stream,
-             (kernel_matrix_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(N, M, Jr, Jc, ar, cr, ac, bc, cc, dc, x1, x2, K_out)));
+             (launch_k(kernel_matrix_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, N, M, Jr, Jc, ar, cr, ac, bc, cc, dc, x1, x2, K_out)));
   return C2B_OK;
 }
 
@@ -153,9 +156,9 @@ int c2b_predict_variance(int64_t N, int64_t M, int32_t Jr, int32_t Jc, const dou
   const int64_t rows   = (N + nchunk - 1) / nchunk;
   dim3 grid((unsigned)((M + 31) / 32), (unsigned)nchunk);
   C2B_LAUNCH("variance_partial_kernel", stream,
-             (variance_partial_kernel<<<grid, 32 * kVarRows, 0, stream>>>(N, M, rows, Jr, Jc, ar, cr, ac, bc, cc, dc, x1, x2, Z, (double *)sc.ptr)));
+             (launch_k(variance_partial_kernel, grid, 32 * kVarRows, 0, stream, N, M, rows, Jr, Jc, ar, cr, ac, bc, cc, dc, x1, x2, Z, (double *)sc.ptr)));
   C2B_LAUNCH("variance_final_kernel", stream,
-             (variance_final_kernel<<<(unsigned)((M + 255) / 256), 256, 0, stream>>>(M, nchunk, Jr, Jc, ar, ac, (const double *)sc.ptr, var_out)));
+             (launch_k(variance_final_kernel, (unsigned)((M + 255) / 256), 256, 0, stream, M, nchunk, Jr, Jc, ar, ac, (const double *)sc.ptr, var_out)));
   return C2B_OK;
 }
 

@@ -149,6 +149,7 @@ static int sweep_rev_entry(int64_t N, int J, int K, int64_t batch, const double 
 // Z[b][n][k] = Y[b][n][k] * sqrt(d[b][n]): the first half of dot_tril (python/celerite2/numpy.py:100-102)
 static __global__ void __launch_bounds__(256) scale_sqrt_rows_kernel(int64_t total, int64_t NK, int K, int64_t y_bs, const double *d,
                                                                      const double *Y, double *Z) {
+  pdl_prologue();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t b = i / NK, r = i - b * NK;
     Z[i]            = Y[b * y_bs + r] * sqrt(d[i / K]);
@@ -180,7 +181,7 @@ int c2b_dot_tril(int64_t N, int32_t J, int32_t K, int64_t batch, const double *t
   int64_t blocks = (total + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
   C2B_LAUNCH("scale_sqrt_rows_kernel", (cudaStream_t)stream,
-             (scale_sqrt_rows_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(total, NK, K, (flags & C2B_SHARED_Y) ? 0 : NK, d, Y, Z)));
+             (launch_k(scale_sqrt_rows_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, total, NK, K, (flags & C2B_SHARED_Y) ? 0 : NK, d, Y, Z)));
   // z <- L z in place: the sweep keeps the previous INPUT row (internal.hpp:134-141), so aliasing Y and Z is exact
   return sweep_entry<false, true>(N, J, K, batch, t, c, U, W, Z, Z, nullptr, flags & ~C2B_SHARED_Y, scratch, scratch_bytes, stream);
 }

@@ -97,6 +97,7 @@ C2B_DEV RotMode rot_mode(double k, double Q, double period, double A) {
 // 5 (rotation: sigma, period, Q0, dQ, f)
 static __global__ void __launch_bounds__(128) term_fwd_kernel(int kind, int64_t batch, const double *params, double eps, int under,
                                                               TermSlots s, int32_t *bad) {
+  pdl_prologue();
   const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
   switch (kind) {
@@ -132,6 +133,7 @@ static __global__ void __launch_bounds__(128) term_fwd_kernel(int kind, int64_t 
 
 static __global__ void __launch_bounds__(128) term_rev_kernel(int kind, int64_t batch, const double *params, double eps, int under,
                                                               TermSlots s, double *bparams) {
+  pdl_prologue();
   const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
   switch (kind) {
@@ -219,6 +221,7 @@ struct TermGrad {
 };
 
 static __global__ void __launch_bounds__(128) term_product_kernel(int64_t batch, TermIn x, TermIn y, TermSlots s) {
+  pdl_prologue();
   const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
   const double *xar = x.ar + b * x.Jr, *xcr = x.cr + b * x.Jr, *xac = x.ac + b * x.Jc, *xbc = x.bc + b * x.Jc, *xcc = x.cc + b * x.Jc,
@@ -243,6 +246,7 @@ static __global__ void __launch_bounds__(128) term_product_kernel(int64_t batch,
 // adjoint: cotangents of the product's coefficients (in s, read) -> cotangents of both factors (gx, gy: overwritten)
 static __global__ void __launch_bounds__(128) term_product_rev_kernel(int64_t batch, TermIn x, TermIn y, TermSlots s, TermGrad gx,
                                                                       TermGrad gy) {
+  pdl_prologue();
   const int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
   const double *xar = x.ar + b * x.Jr, *xac = x.ac + b * x.Jc, *xbc = x.bc + b * x.Jc;
@@ -317,7 +321,7 @@ int c2b_term_coefficients(int32_t kind, int64_t batch, const double *params, dou
   C2B_REQUIRE((nr == 0 || (ar && cr)) && (nc == 0 || (ac && bc && cc && dc)), "null coefficient pointer");
   TermSlots s{Jr_total, Jc_total, r_off, c_off, ar, cr, ac, bc, cc, dc};
   C2B_LAUNCH("term_fwd_kernel", (cudaStream_t)stream,
-             (term_fwd_kernel<<<(unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream>>>(kind, batch, params, eps, underdamped, s, bad)));
+             (launch_k(term_fwd_kernel, (unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream, kind, batch, params, eps, underdamped, s, bad)));
   return C2B_OK;
 }
 
@@ -335,7 +339,7 @@ int c2b_term_coefficients_rev(int32_t kind, int64_t batch, const double *params,
   TermSlots s{Jr_total, Jc_total, r_off, c_off, (double *)b_ar, (double *)b_cr, (double *)b_ac, (double *)b_bc, (double *)b_cc,
               (double *)b_dc};
   C2B_LAUNCH("term_rev_kernel", (cudaStream_t)stream,
-             (term_rev_kernel<<<(unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream>>>(kind, batch, params, eps, underdamped, s, b_params)));
+             (launch_k(term_rev_kernel, (unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream, kind, batch, params, eps, underdamped, s, b_params)));
   return C2B_OK;
 }
 
@@ -351,7 +355,7 @@ int c2b_term_product(int64_t batch, int32_t Jr1, int32_t Jc1, const double *ar1,
   TermIn x{Jr1, Jc1, ar1, cr1, ac1, bc1, cc1, dc1}, y{Jr2, Jc2, ar2, cr2, ac2, bc2, cc2, dc2};
   TermSlots s{Jr, Jc, 0, 0, ar, cr, ac, bc, cc, dc};
   C2B_LAUNCH("term_product_kernel", (cudaStream_t)stream,
-             (term_product_kernel<<<(unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream>>>(batch, x, y, s)));
+             (launch_k(term_product_kernel, (unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream, batch, x, y, s)));
   return C2B_OK;
 }
 
@@ -369,7 +373,7 @@ int c2b_term_product_rev(int64_t batch, int32_t Jr1, int32_t Jc1, const double *
   TermSlots s{Jr, Jc, 0, 0, (double *)b_ar, (double *)b_cr, (double *)b_ac, (double *)b_bc, (double *)b_cc, (double *)b_dc};
   TermGrad gx{g1_ar, g1_cr, g1_ac, g1_bc, g1_cc, g1_dc}, gy{g2_ar, g2_cr, g2_ac, g2_bc, g2_cc, g2_dc};
   C2B_LAUNCH("term_product_rev_kernel", (cudaStream_t)stream,
-             (term_product_rev_kernel<<<(unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream>>>(batch, x, y, s, gx, gy)));
+             (launch_k(term_product_rev_kernel, (unsigned)((batch + 127) / 128), 128, 0, (cudaStream_t)stream, batch, x, y, s, gx, gy)));
   return C2B_OK;
 }
 

@@ -78,6 +78,39 @@ struct OpScope {
     g_op = prev;
   }
 };
+// ---- programmatic dependent launch ---------------------------------------------------------------------------
+// An evaluation is a chain of ~35 dependent kernels.  Every kernel opens with pdl_prologue(): it lets the NEXT kernel of
+// the stream be scheduled right away and then waits until the PREVIOUS kernel has completed and flushed, before it
+// touches any memory.  A launch that carries the matching attribute may therefore be set up while its predecessor is
+// still running; without the attribute both instructions are no-ops and the launch is an ordinary stream-ordered one.
+// Measured (r02t / r02u; attribute on every launch against none): c5 (512 series x 27 chunks) 11.03 -> 10.08 ms, c1 no
+// change, c2 (one series, 7,104 chunks) 0.937 -> 0.972 ms, c3 (8,192 whole series, 512 CTAs) 30.4 -> 34.5 ms -- CTAs of
+// a wave-filling kernel that become resident early, beside the scan's CTAs or in the slots a 512-CTA grid leaves free,
+// end up unevenly spread over the SMs; on the small kernels alone c2 0.948 ms.  Hence the default: the attribute is set
+// for the ops of a CHUNKED BATCH only (g_pdl_wave, set where the op's chunk plan is made).  C2B_PDL=0 never, 2 always.
+C2B_DEV void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+int pdl_mode();
+extern thread_local bool g_pdl_wave;
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args &&...args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim          = grid;
+  cfg.blockDim         = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream           = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id                                         = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs                                        = at;
+  const int mode                                   = pdl_mode();
+  cfg.numAttrs                                     = (mode >= 2 || (mode == 1 && g_pdl_wave)) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 #define C2B_LAUNCH(name, stream, ...)                                                                                                     \
   do {                                                                                                                                    \
     if (c2b::g_profile_on) c2b::prof_begin(name, stream);                                                                                 \

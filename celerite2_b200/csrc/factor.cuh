@@ -50,6 +50,7 @@ C2B_DEV void factor_fetch_row(RP &rp, int J, int64_t n, const double *t, const d
 
 template <int JT>
 __global__ void factor_apply_kernel(FactorArgs g) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : g.J;
@@ -139,6 +140,7 @@ __global__ void factor_apply_kernel(FactorArgs g) {
 
 template <int JT>
 __global__ void factor_summary_kernel(FactorArgs g) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : g.J;
@@ -376,6 +378,7 @@ C2B_DEV void factor_rev_rows(int J, int64_t N, int64_t n0, int64_t n1, const dou
 
 template <int JT>
 __global__ void factor_rev_apply_kernel(FactorRevArgs g) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : g.J;
@@ -417,6 +420,7 @@ __global__ void factor_rev_apply_kernel(FactorRevArgs g) {
 //   col == J: B = the chunk run from G = 0 without outputs
 template <int JT>
 __global__ void factor_rev_summary_kernel(FactorRevArgs g) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : g.J;
@@ -488,6 +492,7 @@ __global__ void factor_rev_summary_kernel(FactorRevArgs g) {
 // summary, one thread per (series, chunk): M and B in a single pass over the rows
 template <int JT>
 __global__ void factor_rev_summary1_kernel(FactorRevArgs g) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : g.J;

@@ -196,6 +196,7 @@ struct FoldRing {
 template <class Mon>
 __global__ void __launch_bounds__(kFoldMaxThreads) fold_groups_kernel(int J_, int K, FoldPlan fp, double *nodes_all, double *states_all,
                                                                      double *heads_all) {
+  pdl_prologue();
   using F = Fold<Mon>;
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double fsm[];
@@ -252,6 +253,7 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_groups_kernel(int J_, in
 template <class Mon>
 __global__ void __launch_bounds__(kFoldMaxThreads) fold_top_kernel(int J_, int K, FoldPlan fp, bool want_states, bool want_root,
                                                                   double *nodes_all, double *states_all, const double *init) {
+  pdl_prologue();
   using F = Fold<Mon>;
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double fsm[];
@@ -313,6 +315,7 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_top_kernel(int J_, int K
 // barriers inside `lift` line up.
 template <class Mon>
 __global__ void __launch_bounds__(256) fold_finish_kernel(int J_, int K, FoldPlan fp, double *states_all, const double *heads_all) {
+  pdl_prologue();
   using F = Fold<Mon>;
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double fsm[];
@@ -399,14 +402,14 @@ static inline int run_fold(int J, int K, int64_t batch, int64_t leaves, int64_t 
   const unsigned ns = (unsigned)fp.nslices;
   if (mode != 2)
     C2B_LAUNCH("fold_groups_kernel", stream,
-               (fold_groups_kernel<Mon><<<dim3((unsigned)(batch * fp.ng), ns), fp.threads, fp.smemA, stream>>>(J, K, fp, nodes, states, heads)));
+               (launch_k(fold_groups_kernel<Mon>, dim3((unsigned)(batch * fp.ng), ns), fp.threads, fp.smemA, stream, J, K, fp, nodes, states, heads)));
   C2B_LAUNCH("fold_top_kernel", stream,
-             (fold_top_kernel<Mon><<<dim3((unsigned)batch, ns), fp.threads, fp.smemA, stream>>>(J, K, fp, mode != 1, mode == 1, nodes, states, init)));
+             (launch_k(fold_top_kernel<Mon>, dim3((unsigned)batch, ns), fp.threads, fp.smemA, stream, J, K, fp, mode != 1, mode == 1, nodes, states, init)));
   if (mode != 1) {
     const int cpb     = 256 / fp.fthreads;
     const int64_t per = (fp.C + cpb - 1) / cpb;
     C2B_LAUNCH("fold_finish_kernel", stream,
-               (fold_finish_kernel<Mon><<<dim3((unsigned)(batch * per), ns), 256, fp.smemC, stream>>>(J, K, fp, states, heads)));
+               (launch_k(fold_finish_kernel<Mon>, dim3((unsigned)(batch * per), ns), 256, fp.smemC, stream, J, K, fp, states, heads)));
   }
   return C2B_OK;
 }

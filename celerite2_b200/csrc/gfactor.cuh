@@ -24,6 +24,7 @@ struct FactorTile {
 // aligned (the launcher checks), otherwise the DIRECT form runs.
 template <int J, bool DIRECT = false, bool BULK = false>
 __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_kernel(FactorArgs g) {
+  pdl_prologue();
   static_assert(!(DIRECT && BULK), "one way of writing the workspace rows");
   constexpr int BR = 2;  // rows per bulk store
   constexpr int G  = GroupOf<J>::G;
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
   issue(0);
   issue(1);
   bool alive = has;
+  int bsel   = 0;  // BULK: the buffer being filled
   for (int k = 0; k < ttrips; ++k) {
     cp_async_wait<1>();
     __syncwarp();
@@ -130,7 +132,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
         }
       } else if (BULK) {
         if (S && act) {
-          double *dst = sbuf + ((r / BR) & 1) * (BR * J * J) + (r % BR) * J * J + J * c;
+          double *dst = sbuf + bsel * (BR * J * J) + (r % BR) * J * J + J * c;
 #pragma unroll
           for (int j = 0; j + 1 < J; j += 2) *reinterpret_cast<double2 *>(dst + j) = make_double2(St[j], St[j + 1]);
         }
@@ -165,12 +167,13 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
         // the barrier after the exchange of w made the buffer's rows visible; rows past a failure stay unwritten
         if (c == 0) {
           if (S && stored > 0) {
-            bulk_store(S + (nt + r + 1 - BR) * (int64_t)(J * J), sbuf + ((r / BR) & 1) * (BR * J * J), (uint32_t)(stored * J * J * sizeof(double)));
+            bulk_store(S + (nt + r + 1 - BR) * (int64_t)(J * J), sbuf + bsel * (BR * J * J), (uint32_t)(stored * J * J * sizeof(double)));
           }
           bulk_commit();
           bulk_wait_read<1>();  // the other buffer (handed over BR rows ago) may be written again
         }
         stored = 0;
+        bsel ^= 1;  // (tiles of two rows, J > 8, hand over one buffer per tile: the choice cannot hang on r)
         __syncwarp();
       }
       if (!DIRECT && !BULK && (r + 1) % SR == 0) {
@@ -198,6 +201,7 @@ __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_apply_
 // tile buffer: U[R*J] V[R*J] | t[R+2] a[R]
 template <int J>
 __global__ void __launch_bounds__(kGroupThreads, C2B_MINB_FACTOR) gfactor_summary_kernel(FactorArgs g) {
+  pdl_prologue();
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreads / G;
   constexpr int R  = FactorTile<J>::R;

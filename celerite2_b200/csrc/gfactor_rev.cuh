@@ -18,6 +18,7 @@ constexpr int kGroupThreadsR = 64;
 // in by one bulk copy of the TMA engine per group and tile (mbarrier-tracked) instead of R * J * J / 2 16-byte cp.async.
 template <int J, bool WRITE, bool BULK = false>
 __global__ void __launch_bounds__(kGroupThreadsR, C2B_MINB_FREV) gfactor_rev_kernel(FactorRevArgs g) {
+  pdl_prologue();
   static_assert(!BULK || (WRITE && J % 2 == 0), "bulk loads are for the workspace rows of the apply pass");
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreadsR / G;

@@ -15,6 +15,7 @@ constexpr int kTileRows = 8;  // rows per staged tile (group.cuh)
 // tile buffer: A[R*J] B[R*J] | t[R+2] y[R] z_old[R]
 template <int J, bool SOLVE, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_apply_kernel(SweepArgs a) {
+  pdl_prologue();
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -117,6 +118,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_apply_k
 // tile buffer: A[R*J] B[R*J] | t[R+2] y[R]; plus one R x J block per group for the propagators of the tile
 template <int J, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_summary_kernel(SweepArgs a) {
+  pdl_prologue();
   constexpr int G  = GroupOf<J + 1>::G;  // J + 1 columns
   constexpr int GP = kGroupThreadsS / G;
   constexpr int R  = kTileRows;
@@ -220,6 +222,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_summary
 // tile buffer: B[R*J] | t[R+2] y[R]
 template <int J, bool LOWER, bool STORE = false>
 __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_msummary_kernel(SweepArgs a) {
+  pdl_prologue();
   constexpr int G  = GroupOf<J>::G;
   constexpr int GP = kGroupThreadsS / G;
   constexpr int R  = kTileRows;
@@ -308,6 +311,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_msummar
 // tile buffer: A[R*J] | t[R+2] bZ[R]
 template <int J, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_msummary_kernel(SweepRevArgs a) {
+  pdl_prologue();
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -393,6 +397,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_msu
 // tile buffer: A[R*J] B[R*J] F[R*J] | t[R+2] bZ[R] (Z or Y)[R]
 template <int J, bool SOLVE, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_apply_kernel(SweepRevArgs a) {
+  pdl_prologue();
   constexpr int G   = GroupOf<J>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -521,6 +526,7 @@ __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_app
 // tile buffer: A[R*J] B[R*J] | t[R+2] bZ[R]; plus the R x J propagator block
 template <int J, bool LOWER>
 __global__ void __launch_bounds__(kGroupThreadsS, C2B_MINB_SWEEP) gsweep_rev_summary_kernel(SweepRevArgs a) {
+  pdl_prologue();
   constexpr int G   = GroupOf<J + 1>::G;
   constexpr int GP  = kGroupThreadsS / G;
   constexpr int R   = kTileRows;
@@ -657,6 +663,7 @@ __host__ __device__ inline size_t csweep_smem_doubles(int yw) {
 
 template <int J, bool LOWER, bool SUMMARY>
 __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a) {
+  pdl_prologue();
   constexpr int R  = kTileRows;
   constexpr int oB = R * J, oT = 2 * R * J, oY = oT + ((R + 2 + 1) & ~1);
   extern __shared__ __align__(16) double cs_smem[];
@@ -784,6 +791,7 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
 // =================================================================================================================
 template <int J, bool LOWER, bool SUMMARY>
 __global__ void __launch_bounds__(128) csweep_kernel(SweepArgs a) {
+  pdl_prologue();
   static_assert(J <= 32, "one lane per row element");
   const int lane       = threadIdx.x & 31;
   const int ncol       = SUMMARY ? J + a.K : a.K;

@@ -25,7 +25,7 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
       g.node_stride = sb.node_stride;
     }
     if ((phase == 0 && g.C > 1) || phase == 1)
-      C2B_LAUNCH("gfactor_summary_kernel", stream, gfactor_summary_kernel<JT><<<grid, kGroupThreads, 0, stream>>>(g));
+      C2B_LAUNCH("gfactor_summary_kernel", stream, launch_k(gfactor_summary_kernel<JT>, grid, kGroupThreads, 0, stream, g));
     if (phase == 1) {
       if ((rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
       return seg_export_root<Lft<JT>>(g.J, 1, g.C, sb.nodes, g.seg.summary_out, stream);
@@ -47,14 +47,14 @@ static int launch_factor_group(FactorArgs &g, const ScanBuffers &sb, cudaStream_
     static const bool bulk_s = getenv("C2B_S_BULK") == nullptr || atoi(getenv("C2B_S_BULK")) != 0;
     if constexpr (JT % 2 == 0) {
       if (bulk_s && g.C > 1 && g.S && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
-        C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, false, true><<<grid, kGroupThreads, 0, stream>>>(g)));
+        C2B_LAUNCH("gfactor_apply_kernel", stream, (launch_k(gfactor_apply_kernel<JT, false, true>, grid, kGroupThreads, 0, stream, g)));
         return C2B_OK;
       }
     }
     if (direct_s && g.S)
-      C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, true><<<grid, kGroupThreads, 0, stream>>>(g)));
+      C2B_LAUNCH("gfactor_apply_kernel", stream, (launch_k(gfactor_apply_kernel<JT, true>, grid, kGroupThreads, 0, stream, g)));
     else
-      C2B_LAUNCH("gfactor_apply_kernel", stream, (gfactor_apply_kernel<JT, false><<<grid, kGroupThreads, 0, stream>>>(g)));
+      C2B_LAUNCH("gfactor_apply_kernel", stream, (launch_k(gfactor_apply_kernel<JT, false>, grid, kGroupThreads, 0, stream, g)));
   }
   return C2B_OK;
 }
@@ -74,14 +74,14 @@ int launch_factor(FactorArgs &g, const ScanBuffers &sb, cudaStream_t stream) {
     g.node_stride = sb.node_stride;
     rcs = staged_shape(factor_summary_kernel<JT>, g.batch * g.C, JT > 0, kFactorSlots, FactorRow<JT>::ROWD, &grid, &block, &smem);
     if (rcs) return rcs;
-    C2B_LAUNCH("factor_summary_kernel", stream, factor_summary_kernel<JT><<<grid, block, smem, stream>>>(g));
+    C2B_LAUNCH("factor_summary_kernel", stream, launch_k(factor_summary_kernel<JT>, grid, block, smem, stream, g));
     int rc = run_scan<Lft<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
   rcs = staged_shape(factor_apply_kernel<JT>, g.batch * g.C, JT > 0, kFactorSlots, FactorRow<JT>::ROWD, &grid, &block, &smem);
   if (rcs) return rcs;
-  C2B_LAUNCH("factor_apply_kernel", stream, factor_apply_kernel<JT><<<grid, block, smem, stream>>>(g));
+  C2B_LAUNCH("factor_apply_kernel", stream, launch_k(factor_apply_kernel<JT>, grid, block, smem, stream, g));
   return C2B_OK;
 }
 
@@ -97,7 +97,7 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
       g.node_stride = sb.node_stride;
     }
     if ((phase == 0 && g.C > 1) || phase == 1)
-      C2B_LAUNCH("gfactor_rev_summary_kernel", stream, gfactor_rev_kernel<JT, false><<<grid, kGroupThreadsR, 0, stream>>>(g));
+      C2B_LAUNCH("gfactor_rev_summary_kernel", stream, launch_k(gfactor_rev_kernel<JT, false>, grid, kGroupThreadsR, 0, stream, g));
     if (phase == 1) {
       if ((rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
       return seg_export_root<Cong<JT>>(g.J, 1, g.C, sb.nodes, g.seg.summary_out, stream);
@@ -115,13 +115,13 @@ static int launch_factor_rev_group(FactorRevArgs &g, const ScanBuffers &sb, doub
     bool launched            = false;
     if constexpr (JT % 2 == 0) {
       if (bulk_s && (reinterpret_cast<uintptr_t>(g.S) & 15) == 0) {
-        C2B_LAUNCH("gfactor_rev_apply_kernel", stream, (gfactor_rev_kernel<JT, true, true><<<grid, kGroupThreadsR, 0, stream>>>(g)));
+        C2B_LAUNCH("gfactor_rev_apply_kernel", stream, (launch_k(gfactor_rev_kernel<JT, true, true>, grid, kGroupThreadsR, 0, stream, g)));
         launched = true;
       }
     }
-    if (!launched) C2B_LAUNCH("gfactor_rev_apply_kernel", stream, gfactor_rev_kernel<JT, true><<<grid, kGroupThreadsR, 0, stream>>>(g));
+    if (!launched) C2B_LAUNCH("gfactor_rev_apply_kernel", stream, launch_k(gfactor_rev_kernel<JT, true>, grid, kGroupThreadsR, 0, stream, g));
     C2B_LAUNCH("rev_finalize_kernel", stream,
-               rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
+               launch_k(rev_finalize_kernel, dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream, g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
     if (phase == 2 && g.seg.edge_out)
       C2B_CUDA(cudaMemcpyAsync(g.seg.edge_out, g.bt_edge, sizeof(double), cudaMemcpyDeviceToDevice, stream));
   }
@@ -143,15 +143,15 @@ int launch_factor_rev(FactorRevArgs &g, const ScanBuffers &sb, double *bc, cudaS
     g.node_stride = sb.node_stride;
     rcs = staged_shape(factor_rev_summary1_kernel<JT>, g.batch * g.C, JT > 0, kFactorRevSlots, FactorRevRow<JT>::ROWD, &grid, &block, &smem);
     if (rcs) return rcs;
-    C2B_LAUNCH("factor_rev_summary1_kernel", stream, factor_rev_summary1_kernel<JT><<<grid, block, smem, stream>>>(g));
+    C2B_LAUNCH("factor_rev_summary1_kernel", stream, launch_k(factor_rev_summary1_kernel<JT>, grid, block, smem, stream, g));
     int rc = run_scan<Cong<JT>>(g.J, 1, g.batch, g.C, sb.nodes, sb.states, nullptr, stream);
     if (rc) return rc;
     g.carry = sb.states;
   }
   rcs = staged_shape(factor_rev_apply_kernel<JT>, g.batch * g.C, JT > 0, kFactorRevSlots, FactorRevRow<JT>::ROWD, &grid, &block, &smem);
   if (rcs) return rcs;
-  C2B_LAUNCH("factor_rev_apply_kernel", stream, factor_rev_apply_kernel<JT><<<grid, block, smem, stream>>>(g));
-  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream>>>(g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
+  C2B_LAUNCH("factor_rev_apply_kernel", stream, launch_k(factor_rev_apply_kernel<JT>, grid, block, smem, stream, g));
+  C2B_LAUNCH("rev_finalize_kernel", stream, launch_k(rev_finalize_kernel, dim3((unsigned)((g.C + 1023) / 1024), (unsigned)g.batch), 1024, 0, stream, g.N, g.C, g.L, g.J, true, g.bc_part, g.bt_edge, g.bt, bc, g.acc != 0));
   return C2B_OK;
 }
 

@@ -22,12 +22,12 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
     if (a.C > 1) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
-      C2B_LAUNCH("gsweep_msummary_kernel", stream, gsweep_msummary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      C2B_LAUNCH("gsweep_msummary_kernel", stream, launch_k(gsweep_msummary_kernel<JT, LOWER>, grid, kGroupThreadsS, 0, stream, a));
       int rc = run_scan<DiagV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
-    C2B_LAUNCH("gsweep_apply_kernel", stream, gsweep_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+    C2B_LAUNCH("gsweep_apply_kernel", stream, launch_k(gsweep_apply_kernel<JT, SOLVE, LOWER>, grid, kGroupThreadsS, 0, stream, a));
   }
   if constexpr (JT > 0 && JT <= 16 && SOLVE) {
     const int phase = a.seg.phase;
@@ -39,7 +39,7 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
     if ((phase == 0 && a.C > 1) || phase == 1) {
       constexpr int GPS   = kGroupThreadsS / GroupOf<JT + 1>::G;
       const unsigned grid = (unsigned)((a.batch * a.C + GPS - 1) / GPS);
-      C2B_LAUNCH("gsweep_summary_kernel", stream, gsweep_summary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      C2B_LAUNCH("gsweep_summary_kernel", stream, launch_k(gsweep_summary_kernel<JT, LOWER>, grid, kGroupThreadsS, 0, stream, a));
     }
     if (phase == 1) {
       if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
@@ -55,7 +55,7 @@ static int launch_sweep_group(SweepArgs &a, const ScanBuffers &sb, cudaStream_t 
     }
     constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
-    C2B_LAUNCH("gsweep_apply_kernel", stream, gsweep_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+    C2B_LAUNCH("gsweep_apply_kernel", stream, launch_k(gsweep_apply_kernel<JT, SOLVE, LOWER>, grid, kGroupThreadsS, 0, stream, a));
   }
   return C2B_OK;
 }
@@ -68,14 +68,14 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     if (a.C > 1) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
-      C2B_LAUNCH("gsweep_rev_msummary_kernel", stream, gsweep_rev_msummary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      C2B_LAUNCH("gsweep_rev_msummary_kernel", stream, launch_k(gsweep_rev_msummary_kernel<JT, LOWER>, grid, kGroupThreadsS, 0, stream, a));
       int rc = run_scan<DiagV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
-    C2B_LAUNCH("gsweep_rev_apply_kernel", stream, gsweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+    C2B_LAUNCH("gsweep_rev_apply_kernel", stream, launch_k(gsweep_rev_apply_kernel<JT, SOLVE, LOWER>, grid, kGroupThreadsS, 0, stream, a));
     C2B_LAUNCH("rev_finalize_kernel", stream,
-               rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
+               launch_k(rev_finalize_kernel, dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream, a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   }
   if constexpr (JT > 0 && JT <= 16 && SOLVE) {
     const int phase = a.seg.phase;
@@ -87,7 +87,7 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     if ((phase == 0 && a.C > 1) || phase == 1) {
       constexpr int GPS   = kGroupThreadsS / GroupOf<JT + 1>::G;
       const unsigned grid = (unsigned)((a.batch * a.C + GPS - 1) / GPS);
-      C2B_LAUNCH("gsweep_rev_summary_kernel", stream, gsweep_rev_summary_kernel<JT, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+      C2B_LAUNCH("gsweep_rev_summary_kernel", stream, launch_k(gsweep_rev_summary_kernel<JT, LOWER>, grid, kGroupThreadsS, 0, stream, a));
     }
     if (phase == 1) {
       if ((rc = run_scan<AffV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream, 1))) return rc;
@@ -103,9 +103,9 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
     }
     constexpr int GP    = kGroupThreadsS / GroupOf<JT>::G;
     const unsigned grid = (unsigned)((a.batch * a.C + GP - 1) / GP);
-    C2B_LAUNCH("gsweep_rev_apply_kernel", stream, gsweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, kGroupThreadsS, 0, stream>>>(a));
+    C2B_LAUNCH("gsweep_rev_apply_kernel", stream, launch_k(gsweep_rev_apply_kernel<JT, SOLVE, LOWER>, grid, kGroupThreadsS, 0, stream, a));
     C2B_LAUNCH("rev_finalize_kernel", stream,
-               rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
+               launch_k(rev_finalize_kernel, dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream, a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
     if (phase == 2 && a.seg.edge_out)  // the chunk at the far end of the sweep owes its term to the neighbouring segment
       C2B_CUDA(cudaMemcpyAsync(a.seg.edge_out, a.bt_edge + (LOWER ? 0 : a.C - 1), sizeof(double), cudaMemcpyDeviceToDevice, stream));
   }
@@ -126,14 +126,14 @@ static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_
       a.node_stride = sb.node_stride;
       const int nt  = threads_for(JT + a.K);
       const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
-      C2B_LAUNCH("csweep_summary_kernel", stream, (csweep_tile_kernel<JT, LOWER, true><<<grid, nt, smem, stream>>>(a)));
+      C2B_LAUNCH("csweep_summary_kernel", stream, (launch_k(csweep_tile_kernel<JT, LOWER, true>, grid, nt, smem, stream, a)));
       int rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
     const int nt      = threads_for(a.K);
     const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
-    C2B_LAUNCH("csweep_apply_kernel", stream, (csweep_tile_kernel<JT, LOWER, false><<<grid, nt, smem, stream>>>(a)));
+    C2B_LAUNCH("csweep_apply_kernel", stream, (launch_k(csweep_tile_kernel<JT, LOWER, false>, grid, nt, smem, stream, a)));
   }
   return C2B_OK;
 }
@@ -157,12 +157,12 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
     if (SOLVE && a.K == 1) {
       rcs = staged_shape(sweep_summary1_kernel<JT, LOWER>, a.batch * a.C, JT > 0, kSweepSlots, SweepRow<JT>::ROWD, &grid, &block, &smem);
       if (rcs) return rcs;
-      C2B_LAUNCH("sweep_summary1_kernel", stream, sweep_summary1_kernel<JT, LOWER><<<grid, block, smem, stream>>>(a));
+      C2B_LAUNCH("sweep_summary1_kernel", stream, launch_k(sweep_summary1_kernel<JT, LOWER>, grid, block, smem, stream, a));
     } else {
       rcs = staged_shape(sweep_summary_kernel<JT, SOLVE, LOWER>, a.batch * a.C * ncol, JT > 0, kSweepSlots, SweepRow<JT>::ROWD, &grid,
                          &block, &smem);
       if (rcs) return rcs;
-      C2B_LAUNCH("sweep_summary_kernel", stream, sweep_summary_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
+      C2B_LAUNCH("sweep_summary_kernel", stream, launch_k(sweep_summary_kernel<JT, SOLVE, LOWER>, grid, block, smem, stream, a));
     }
     int rc;
     if (SOLVE)
@@ -174,7 +174,7 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   }
   rcs = staged_shape(sweep_apply_kernel<JT, SOLVE, LOWER>, a.batch * a.C * a.K, JT > 0, kSweepSlots, SweepRow<JT>::ROWD, &grid, &block, &smem);
   if (rcs) return rcs;
-  C2B_LAUNCH("sweep_apply_kernel", stream, sweep_apply_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
+  C2B_LAUNCH("sweep_apply_kernel", stream, launch_k(sweep_apply_kernel<JT, SOLVE, LOWER>, grid, block, smem, stream, a));
   return C2B_OK;
 }
 
@@ -197,12 +197,12 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
       rcs = staged_shape(sweep_rev_summary1_kernel<JT, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
                          &smem);
       if (rcs) return rcs;
-      C2B_LAUNCH("sweep_rev_summary1_kernel", stream, sweep_rev_summary1_kernel<JT, LOWER><<<grid, block, smem, stream>>>(a));
+      C2B_LAUNCH("sweep_rev_summary1_kernel", stream, launch_k(sweep_rev_summary1_kernel<JT, LOWER>, grid, block, smem, stream, a));
     } else {
       rcs = staged_shape(sweep_rev_summary_kernel<JT, SOLVE, LOWER>, a.batch * a.C * ncol, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD,
                          &grid, &block, &smem);
       if (rcs) return rcs;
-      C2B_LAUNCH("sweep_rev_summary_kernel", stream, sweep_rev_summary_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
+      C2B_LAUNCH("sweep_rev_summary_kernel", stream, launch_k(sweep_rev_summary_kernel<JT, SOLVE, LOWER>, grid, block, smem, stream, a));
     }
     int rc;
     if (SOLVE)
@@ -215,8 +215,8 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
   rcs = staged_shape(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
                      &smem);
   if (rcs) return rcs;
-  C2B_LAUNCH("sweep_rev_apply_kernel", stream, sweep_rev_apply_kernel<JT, SOLVE, LOWER><<<grid, block, smem, stream>>>(a));
-  C2B_LAUNCH("rev_finalize_kernel", stream, rev_finalize_kernel<<<dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream>>>(a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
+  C2B_LAUNCH("sweep_rev_apply_kernel", stream, launch_k(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, grid, block, smem, stream, a));
+  C2B_LAUNCH("rev_finalize_kernel", stream, launch_k(rev_finalize_kernel, dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream, a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   return C2B_OK;
 }
 
@@ -229,12 +229,12 @@ int launch_gm_states(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
     if (a.C > 1) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
-      C2B_LAUNCH("gsweep_msummary_kernel", stream, (gsweep_msummary_kernel<JT, LOWER, false><<<grid, kGroupThreadsS, 0, stream>>>(a)));
+      C2B_LAUNCH("gsweep_msummary_kernel", stream, (launch_k(gsweep_msummary_kernel<JT, LOWER, false>, grid, kGroupThreadsS, 0, stream, a)));
       int rc = run_scan<DiagV<JT>>(a.J, 1, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
-    C2B_LAUNCH("gsweep_states_kernel", stream, (gsweep_msummary_kernel<JT, LOWER, true><<<grid, kGroupThreadsS, 0, stream>>>(a)));
+    C2B_LAUNCH("gsweep_states_kernel", stream, (launch_k(gsweep_msummary_kernel<JT, LOWER, true>, grid, kGroupThreadsS, 0, stream, a)));
     return C2B_OK;
   } else {
     return C2B_ERR_INVALID_ARGUMENT;

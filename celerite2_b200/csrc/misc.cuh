@@ -25,6 +25,7 @@ C2B_DEV int col_sin(int layout, int Jr, int Jc, int j) { return layout ? Jr + 2 
 constexpr int kAsmThreads = 128;
 
 __global__ void __launch_bounds__(kAsmThreads) assemble_kernel(AsmArgs g) {
+  pdl_prologue();
   extern __shared__ double asm_tile[];  // U rows [kAsmThreads * J], then V rows
   const int64_t gid0 = (int64_t)blockIdx.x * kAsmThreads;
   const int64_t gid  = gid0 + threadIdx.x;
@@ -89,6 +90,7 @@ struct AsmRevArgs {
 constexpr int kAsmRevThreads = 256;
 
 __global__ void assemble_rev_kernel(AsmRevArgs g) {
+  pdl_prologue();
   extern __shared__ double sh[];  // [nred][kAsmRevThreads]
   const int J     = g.Jr + 2 * g.Jc;
   const int nred  = g.Jr + 3 * g.Jc;
@@ -126,6 +128,7 @@ __global__ void assemble_rev_kernel(AsmRevArgs g) {
 }
 
 __global__ void assemble_rev_final_kernel(AsmRevArgs g) {
+  pdl_prologue();
   // one warp per reduced quantity: lanes stride over the per-CTA partials, fixed-shape shuffle tree (deterministic)
   const int J     = g.Jr + 2 * g.Jc;
   const int nred  = g.Jr + 3 * g.Jc;
@@ -156,6 +159,7 @@ __global__ void assemble_rev_final_kernel(AsmRevArgs g) {
 // ---- log-det / chi^2 (python/celerite2/numpy.py:84-87,104-109) --------------------------------------------------
 constexpr int kRedThreads = 256;
 __global__ void norm_logdet_kernel(int64_t N, const double *d, const double *z, double *bz, double *bd, double *part, int ctas) {
+  pdl_prologue();
   __shared__ double s1[kRedThreads], s2[kRedThreads];
   const int64_t b = blockIdx.y;
   double ld = 0.0, ch = 0.0;
@@ -183,6 +187,7 @@ __global__ void norm_logdet_kernel(int64_t N, const double *d, const double *z, 
   }
 }
 __global__ void norm_logdet_final_kernel(const double *part, int ctas, double *out) {
+  pdl_prologue();
   // warp 0: log-det, warp 1: chi^2
   const int64_t b = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -196,6 +201,7 @@ __global__ void norm_logdet_final_kernel(const double *part, int ctas, double *o
 }
 
 __global__ void add_inplace_kernel(int64_t n, const double *x, double *y) {
+  pdl_prologue();
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] += x[i];
 }
 
@@ -236,6 +242,7 @@ C2B_DEV void gm_rows(const GmArgs &g, int64_t m0, int64_t m1, int k, double *Hs 
 // thread per (chunk, column)
 template <bool UPPER, bool SUMMARY>
 __global__ void gm_scan_kernel(GmArgs g) {
+  pdl_prologue();
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= g.C * g.K) return;
   const int k         = (int)(gid % g.K);
@@ -271,6 +278,7 @@ __global__ void gm_scan_kernel(GmArgs g) {
 // thread per (output row, column)
 template <bool UPPER>
 __global__ void gm_gather_kernel(GmArgs g) {
+  pdl_prologue();
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= g.N * g.K) return;
   const int k     = (int)(gid % g.K);
@@ -296,6 +304,7 @@ __global__ void gm_gather_kernel(GmArgs g) {
 // Copy into the user's workspace exactly the rows the reference writes (forward.hpp:307,313,327 / 369,387).
 template <bool UPPER>
 __global__ void gm_workspace_kernel(GmArgs g) {
+  pdl_prologue();
   const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t JK  = (int64_t)g.J * g.K;
   if (gid >= g.M * JK) return;

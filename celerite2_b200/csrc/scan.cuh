@@ -64,6 +64,7 @@ C2B_DEV void down_node(int J, int K, const Levels &lv, const double *nodes, doub
 // one warp per (series, block of 32 leaves): levels 1..min(5, top)
 template <class Mon>
 __global__ void scan_up_warp(int J_, int K, int64_t batch, Levels lv, double *nodes_all) {
+  pdl_prologue();
   const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
   const int64_t nblk = (lv.count[0] + 31) / 32;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -83,6 +84,7 @@ __global__ void scan_up_warp(int J_, int K, int64_t batch, Levels lv, double *no
 // one CTA per series: levels 6..top up, then top..6 down (leaves states at level 5)
 template <class Mon>
 __global__ void scan_top(int J_, int K, Levels lv, double *nodes_all, double *states_all, const double *init) {
+  pdl_prologue();
   const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
   const int64_t b = blockIdx.x;
   const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
@@ -107,6 +109,7 @@ __global__ void scan_top(int J_, int K, Levels lv, double *nodes_all, double *st
 // one warp per (series, block of 32 leaves): levels min(5, top)..1 down
 template <class Mon>
 __global__ void scan_down_warp(int J_, int K, int64_t batch, Levels lv, const double *nodes_all, double *states_all, const double *init) {
+  pdl_prologue();
   const int J = Mon::kJT ? Mon::kJT : J_;  // compile-time width => unrolled, register-resident
   const int64_t nblk = (lv.count[0] + 31) / 32;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -293,6 +296,7 @@ template <class Mon>
 __global__ void __launch_bounds__(kCoopThreadsMax) pscan_block(int J_, int K, int kb, PLevels pl, int g, int BS, int64_t stride,
                                                               bool do_up, bool do_down, double *nodes_all, double *states_all,
                                                               const double *init) {
+  pdl_prologue();
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double sm_all[];
   const int k0  = blockIdx.y * kb;
@@ -369,6 +373,7 @@ __global__ void __launch_bounds__(kCoopThreadsMax) pscan_block(int J_, int K, in
 template <class Mon, int DIR>
 __global__ void __launch_bounds__(kCoopThreadsMax) scan_block(int J_, int K, int kb, int64_t batch, Levels lv, int lb, int nlev,
                                                              double *nodes_all, double *states_all, const double *init) {
+  pdl_prologue();
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double sm_all[];
   const int k0  = blockIdx.y * kb;                       // my columns: [k0, k0 + kl)
@@ -507,7 +512,7 @@ static inline int run_pscan(int J, int K, int64_t batch, int64_t leaves, double 
   auto launch = [&](const char *name, int g, bool up, bool down) -> int {
     const dim3 grid((unsigned)(batch * ((pl.cnt[g] + pp.BS - 1) / pp.BS)), nslices);
     C2B_LAUNCH(name, stream,
-               (pscan_block<Mon><<<grid, pp.nwarps * 32, pp.smem, stream>>>(J, K, pp.kb, pl, g, pp.BS, lv.total, up, down, nodes, states, init)));
+               (launch_k(pscan_block<Mon>, grid, pp.nwarps * 32, pp.smem, stream, J, K, pp.kb, pl, g, pp.BS, lv.total, up, down, nodes, states, init)));
     return C2B_OK;
   };
   int rc;
@@ -608,22 +613,22 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
     if (mode == 0) {
       for (int q = 0; q + 1 < nb; ++q)
         C2B_LAUNCH("scan_up_block", stream,
-                   (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+                   (launch_k(scan_block<Mon, 0>, grid_of(bases[q]), nwarps * 32, smem, stream, J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
       C2B_LAUNCH("scan_top_block", stream,
-                 (scan_block<Mon, 2><<<grid_of(bases[nb - 1]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
+                 (launch_k(scan_block<Mon, 2>, grid_of(bases[nb - 1]), nwarps * 32, smem, stream, J, K, kb, batch, lv, bases[nb - 1], nlev, nodes, states, init)));
       for (int q = nb - 2; q >= 0; --q)
         C2B_LAUNCH("scan_down_block", stream,
-                   (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+                   (launch_k(scan_block<Mon, 1>, grid_of(bases[q]), nwarps * 32, smem, stream, J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
     } else if (mode == 1) {
       if (top > 0)
         for (int q = 0; q < nb; ++q)
           C2B_LAUNCH("scan_up_block", stream,
-                     (scan_block<Mon, 0><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+                     (launch_k(scan_block<Mon, 0>, grid_of(bases[q]), nwarps * 32, smem, stream, J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
     } else {
       if (top > 0)
         for (int q = nb - 1; q >= 0; --q)
           C2B_LAUNCH("scan_down_block", stream,
-                     (scan_block<Mon, 1><<<grid_of(bases[q]), nwarps * 32, smem, stream>>>(J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
+                     (launch_k(scan_block<Mon, 1>, grid_of(bases[q]), nwarps * 32, smem, stream, J, K, kb, batch, lv, bases[q], nlev, nodes, states, init)));
     }
     return C2B_OK;
   } else {
@@ -635,12 +640,12 @@ static inline int run_scan(int J, int K, int64_t batch, int64_t leaves, double *
   const int64_t warps = batch * nblk;
   const unsigned grid = (unsigned)((warps * 32 + threads - 1) / threads);
   if (lv.nlev > 1) {
-    C2B_LAUNCH("scan_up_warp", stream, scan_up_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes));
+    C2B_LAUNCH("scan_up_warp", stream, launch_k(scan_up_warp<Mon>, grid, threads, 0, stream, J, K, batch, lv, nodes));
   }
   if (lv.nlev - 1 > kWarpLevels) {
-    C2B_LAUNCH("scan_top", stream, scan_top<Mon><<<(unsigned)batch, 256, 0, stream>>>(J, K, lv, nodes, states, init));
+    C2B_LAUNCH("scan_top", stream, launch_k(scan_top<Mon>, (unsigned)batch, 256, 0, stream, J, K, lv, nodes, states, init));
   }
-  C2B_LAUNCH("scan_down_warp", stream, scan_down_warp<Mon><<<grid, threads, 0, stream>>>(J, K, batch, lv, nodes, states, init));
+  C2B_LAUNCH("scan_down_warp", stream, launch_k(scan_down_warp<Mon>, grid, threads, 0, stream, J, K, batch, lv, nodes, states, init));
   return C2B_OK;
   }
 }
@@ -690,6 +695,7 @@ static inline int seg_import_state(int J, int K, int64_t leaves, double *states,
 template <class Mon>
 __global__ void __launch_bounds__(32) seg_carry_kernel(int J_, int K, int nseg, int which, bool descending, const double *summaries,
                                                        double *out) {
+  pdl_prologue();
   const int J = Mon::kJT ? Mon::kJT : J_;
   extern __shared__ __align__(16) double sc_sm[];
   const int es = Mon::esize(J, K), ss = Mon::ssize(J, K);
@@ -714,7 +720,7 @@ static inline int run_seg_carry(int J, int K, int nseg, int which, bool descendi
   if constexpr (Mon::kCoop) {
     const size_t smem = (size_t)(Mon::esize(J, K) + 2 * Mon::ssize(J, K) + Coop<Mon>::wsmem(J, K)) * sizeof(double);
     if (smem > 48 * 1024) C2B_CUDA(cudaFuncSetAttribute(seg_carry_kernel<Mon>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    C2B_LAUNCH("seg_carry_kernel", stream, (seg_carry_kernel<Mon><<<1, 32, smem, stream>>>(J, K, nseg, which, descending, summaries, out)));
+    C2B_LAUNCH("seg_carry_kernel", stream, (launch_k(seg_carry_kernel<Mon>, 1, 32, smem, stream, J, K, nseg, which, descending, summaries, out)));
     return C2B_OK;
   } else {
     set_error("segments of a longer series need a compiled width (J in 1..16)");
@@ -729,6 +735,7 @@ static inline int run_seg_carry(int J, int K, int nseg, int which, bool descendi
 static __global__ void __launch_bounds__(1024) rev_finalize_kernel(int64_t N, int64_t C, int64_t L, int J, bool descending,
                                                                    const double *bc_part, const double *bt_edge, double *bt, double *bc,
                                                                    bool acc_bc) {
+  pdl_prologue();
   const int64_t b = blockIdx.y;
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k < C) {

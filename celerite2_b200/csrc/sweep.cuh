@@ -107,6 +107,7 @@ C2B_DEV void chunk_range(int64_t N, int64_t L, int64_t chunk, int64_t *n0, int64
 // ---- apply: thread per (series, chunk, column) ---------------------------------------------------------------
 template <int JT, bool SOLVE, bool LOWER>
 __global__ void sweep_apply_kernel(SweepArgs a) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : a.J;
@@ -145,6 +146,7 @@ __global__ void sweep_apply_kernel(SweepArgs a) {
 //   matmul : the transition is diag(prod p) = exp(c * (t at chunk entry - t at chunk exit)); only b is swept
 template <int JT, bool SOLVE, bool LOWER>
 __global__ void sweep_summary_kernel(SweepArgs a) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : a.J;
@@ -197,6 +199,7 @@ __global__ void sweep_summary_kernel(SweepArgs a) {
 // one pass over the rows (one row fetch, J+1 independent dependency chains).
 template <int JT, bool LOWER>
 __global__ void sweep_summary1_kernel(SweepArgs a) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : a.J;
@@ -405,6 +408,7 @@ C2B_DEV void sweep_rev_rows(int J, int K, int col, bool first_col, int64_t N, in
 // apply: thread per (series, chunk); loops over the K columns
 template <int JT, bool SOLVE, bool LOWER>
 __global__ void sweep_rev_apply_kernel(SweepRevArgs a) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : a.J;
@@ -448,6 +452,7 @@ __global__ void sweep_rev_apply_kernel(SweepRevArgs a) {
 // summary: thread per (series, chunk, column') -- same column convention as the forward summary
 template <int JT, bool SOLVE, bool LOWER>
 __global__ void sweep_rev_summary_kernel(SweepRevArgs a) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : a.J;
@@ -503,6 +508,7 @@ __global__ void sweep_rev_summary_kernel(SweepRevArgs a) {
 // K == 1 solves, reverse mode: one thread per (series, chunk) carries the J unit columns and the real column.
 template <int JT, bool LOWER>
 __global__ void sweep_rev_summary1_kernel(SweepRevArgs a) {
+  pdl_prologue();
   extern __shared__ double c2b_ring[];
   constexpr int MJ = Width<JT>::MAXJ;
   const int J      = JT ? JT : a.J;
