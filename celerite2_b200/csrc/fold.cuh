@@ -29,12 +29,14 @@ constexpr int kFoldMaxThreads = 512;
 template <class Mon>
 struct Fold {
   static constexpr bool kAffine = false;
+  static constexpr bool kSplit  = false;
 };
 
 // ---- AffV: s -> M s + b, head M (J x J row-major), state J x K (index j + J k) ------------------------------------------
 template <int JT>
 struct Fold<AffV<JT>> {
   static constexpr bool kAffine = true;
+  static constexpr bool kSplit  = true;  // apply and head_step have no barriers inside: two halves of the CTA run them side by side
   __host__ __device__ static int hsize(int J) { return J * J; }
   __host__ __device__ static int scratch(int, int) { return 0; }
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
@@ -44,15 +46,31 @@ struct Fold<AffV<JT>> {
   // column: the kernels keep M TRANSPOSED in shared memory (element (i, j) at j * J + i), or the reads of a warp would sit
   // J doubles apart (16-way bank conflicts at J = 16: r02b, 5 us per step).  head_slot says where entry r of the head goes.
   C2B_DEV static int head_slot(int J, int r) { return (r % J) * J + r / J; }
+  // (compiled widths: the J-term dot products are fully unrolled on two accumulators; a step of the walk is a dependent
+  // instruction stream per thread, r02y: ~200 instructions at ~6 cycles each with the rolled loops)
+  C2B_DEV static double dot_col(int J, const double *mT, int i, const double *x, double init) {
+    if constexpr (JT > 0) {
+      double s0 = init, s1 = 0.0;
+#pragma unroll
+      for (int j = 0; j + 1 < JT; j += 2) {
+        s0 = fma(mT[j * JT + i], x[j], s0);
+        s1 = fma(mT[(j + 1) * JT + i], x[j + 1], s1);
+      }
+      if (JT & 1) s0 = fma(mT[(JT - 1) * JT + i], x[JT - 1], s0);
+      return s0 + s1;
+    } else {
+      double s = init;
+#pragma unroll 4
+      for (int j = 0; j < J; ++j) s = fma(mT[j * J + i], x[j], s);
+      return s;
+    }
+  }
   // sout = M sin + b            (eT: transposed head, then b)
   C2B_DEV static void apply(int tid, int nt, int J, int K, const double *eT, const double *sin, double *sout, double *) {
     const double *b = eT + J * J;
     for (int o = tid; o < J * K; o += nt) {
       const int k = o / J, i = o - k * J;
-      double s    = b[o];
-#pragma unroll 4
-      for (int j = 0; j < J; ++j) s = fma(eT[j * J + i], sin[j + J * k], s);
-      sout[o] = s;
+      sout[o]     = dot_col(J, eT, i, sin + J * k, b[o]);
     }
   }
   // Hout = M Hin   (composition "Hin first, then this element"); H row-major
@@ -60,8 +78,19 @@ struct Fold<AffV<JT>> {
     for (int o = tid; o < J * J; o += nt) {
       const int i = o / J, j = o - i * J;
       double s    = 0.0;
+      if constexpr (JT > 0) {
+        double s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k + 1 < JT; k += 2) {
+          s  = fma(eT[k * JT + i], Hin[k * JT + j], s);
+          s1 = fma(eT[(k + 1) * JT + i], Hin[(k + 1) * JT + j], s1);
+        }
+        if (JT & 1) s = fma(eT[(JT - 1) * JT + i], Hin[(JT - 1) * JT + j], s);
+        s += s1;
+      } else {
 #pragma unroll 4
-      for (int k = 0; k < J; ++k) s = fma(eT[k * J + i], Hin[k * J + j], s);
+        for (int k = 0; k < J; ++k) s = fma(eT[k * J + i], Hin[k * J + j], s);
+      }
       Hout[o] = s;
     }
   }
@@ -69,10 +98,7 @@ struct Fold<AffV<JT>> {
   C2B_DEV static void lift(int tid, int nt, int J, int K, const double *HT, const double *sloc, const double *G, double *out, double *) {
     for (int o = tid; o < J * K; o += nt) {
       const int k = o / J, i = o - k * J;
-      double s    = sloc[o];
-#pragma unroll 4
-      for (int j = 0; j < J; ++j) s = fma(HT[j * J + i], G[j + J * k], s);
-      out[o] = s;
+      out[o]      = dot_col(J, HT, i, G + J * k, sloc[o]);
     }
   }
 };
@@ -81,6 +107,7 @@ struct Fold<AffV<JT>> {
 template <int JT>
 struct Fold<DiagV<JT>> {
   static constexpr bool kAffine = true;
+  static constexpr bool kSplit  = false;
   __host__ __device__ static int hsize(int J) { return J; }
   __host__ __device__ static int scratch(int, int) { return 0; }
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
@@ -102,6 +129,7 @@ struct Fold<DiagV<JT>> {
 template <int JT>
 struct Fold<Cong<JT>> {
   static constexpr bool kAffine = true;
+  static constexpr bool kSplit  = false;
   __host__ __device__ static int hsize(int J) { return J * J; }
   __host__ __device__ static int scratch(int J, int) { return 2 * J * J; }
   C2B_DEV static void head_identity(int tid, int nt, int J, double *H) {
@@ -233,8 +261,17 @@ __global__ void __launch_bounds__(kFoldMaxThreads) fold_groups_kernel(int J_, in
     for (int o = tid; o < ss; o += nt) sl[o < sh ? o : o - sh + sgo] = s[o];
     if (blockIdx.y == 0)
       for (int o = tid; o < hs; o += nt) heads[(int64_t)i * hs + o] = H[o];
-    F::head_step(tid, nt, J, e, H, Hn);
-    F::apply(tid, nt, J, kl, e, s, sn, sc);
+    if (F::kSplit && nt >= 64) {
+      // the head product on the first half of the CTA, the state on the second (whole warps each)
+      const int half = (nt / 64) * 32;
+      if (tid < half)
+        F::head_step(tid, half, J, e, H, Hn);
+      else
+        F::apply(tid - half, nt - half, J, kl, e, s, sn, sc);
+    } else {
+      F::head_step(tid, nt, J, e, H, Hn);
+      F::apply(tid, nt, J, kl, e, s, sn, sc);
+    }
     __syncthreads();  // the slot is free, the new state and head are complete
     issue(i + kFoldDepth);
   }
@@ -370,6 +407,13 @@ static inline FoldPlan fold_plan(int J, int K, int64_t leaves, int64_t stride) {
   };
   int kb = K;
   while (kb > 1 && doubles(kb) * sizeof(double) > 160 * 1024) kb = (kb + 1) / 2;
+  // Slices of about J columns (at least 8): the walks are latency, not work -- narrower slices walk on more SMs at once,
+  // each with a shorter step, and the head product every slice repeats costs no wall time (r02y, c4: J = 16, K = 64:
+  // one slice 0.267 ms of fold kernels per apply_inverse, slices of 32 / 16 / 8 / 4 columns 0.208 / 0.185 / 0.192 / 0.253).
+  // C2B_FOLD_KB overrides.
+  static const int env_kb = getenv("C2B_FOLD_KB") ? atoi(getenv("C2B_FOLD_KB")) : 0;
+  const int want_kb       = env_kb > 0 ? env_kb : (J > 8 ? J : 8);
+  if (want_kb < kb) kb = want_kb;
   const int nsl = (K + kb - 1) / kb;
   kb            = (K + nsl - 1) / nsl;
   fp.kb      = kb;
@@ -377,6 +421,7 @@ static inline FoldPlan fold_plan(int J, int K, int64_t leaves, int64_t stride) {
   const int work = Mon::ssize(J, kb) > hs ? Mon::ssize(J, kb) : hs;
   int th         = (work + 31) / 32 * 32;
   if (th < 64) th = 64;
+  if (F::kSplit) th *= 2;  // (fold_groups_kernel: head product and state on separate halves)
   if (th > kFoldMaxThreads) th = kFoldMaxThreads;
   fp.threads = th;
   int ft     = 32;
