@@ -195,7 +195,8 @@ struct FoldPlan {
   int64_t stride; // per-series stride of nodes / states (elements), = Levels::total
   int kb;         // columns per slice
   int nslices;
-  int threads;    // phases A and B
+  int threads;    // phase A
+  int tthreads;   // phase B: one thread per state entry (r02zb: 64 / 128 threads with more entries each are slower)
   int fthreads;   // phase C: threads per chunk
   size_t smemA, smemC;
 };
@@ -421,6 +422,7 @@ static inline FoldPlan fold_plan(int J, int K, int64_t leaves, int64_t stride) {
   const int work = Mon::ssize(J, kb) > hs ? Mon::ssize(J, kb) : hs;
   int th         = (work + 31) / 32 * 32;
   if (th < 64) th = 64;
+  fp.tthreads = th > kFoldMaxThreads ? kFoldMaxThreads : th;
   if (F::kSplit) th *= 2;  // (fold_groups_kernel: head product and state on separate halves)
   if (th > kFoldMaxThreads) th = kFoldMaxThreads;
   fp.threads = th;
@@ -449,7 +451,7 @@ static inline int run_fold(int J, int K, int64_t batch, int64_t leaves, int64_t 
     C2B_LAUNCH("fold_groups_kernel", stream,
                (launch_k(fold_groups_kernel<Mon>, dim3((unsigned)(batch * fp.ng), ns), fp.threads, fp.smemA, stream, J, K, fp, nodes, states, heads)));
   C2B_LAUNCH("fold_top_kernel", stream,
-             (launch_k(fold_top_kernel<Mon>, dim3((unsigned)batch, ns), fp.threads, fp.smemA, stream, J, K, fp, mode != 1, mode == 1, nodes, states, init)));
+             (launch_k(fold_top_kernel<Mon>, dim3((unsigned)batch, ns), fp.tthreads, fp.smemA, stream, J, K, fp, mode != 1, mode == 1, nodes, states, init)));
   if (mode != 1) {
     const int cpb     = 256 / fp.fthreads;
     const int64_t per = (fp.C + cpb - 1) / cpb;
