@@ -661,7 +661,10 @@ __host__ __device__ inline size_t csweep_smem_doubles(int yw) {
   return (size_t)2 * tb + R * J + J + R;
 }
 
-template <int J, bool LOWER, bool SUMMARY>
+// SOLVE = false: the products (matmul_lower / upper: z_n += a_n . F_n, F fed by the INPUT y_n, forward.hpp:228-271).  Their
+// chunk summary is diagonal-affine (m = the chunk's product of propagators, b = the state reached from zero): K columns,
+// no unit vectors; the thread of column 0 also carries m.
+template <int J, bool LOWER, bool SUMMARY, bool SOLVE = true>
 __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a) {
   pdl_prologue();
   constexpr int R  = kTileRows;
@@ -672,7 +675,8 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
   const int64_t chunk  = blockIdx.x % a.C, b = blockIdx.x / a.C;
   const int64_t n0     = chunk * a.L;
   const int64_t n1     = n0 + a.L < a.N ? n0 + a.L : a.N;
-  const int ncol       = SUMMARY ? J + a.K : a.K;
+  constexpr bool BASIS = SUMMARY && SOLVE;  // J unit-vector columns in front of the real ones
+  const int ncol       = BASIS ? J + a.K : a.K;
   const int yw         = NT < a.K ? NT : a.K;  // widest slice of Y a column group can need
   const int TB         = oY + R * yw;
   double *pb           = cs_smem + 2 * TB;
@@ -695,13 +699,16 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
   for (int q0 = 0; q0 < ncol; q0 += NT) {
     const int q      = q0 + tid;  // my column
     const bool have  = q < ncol;
-    const bool basis = SUMMARY && q < J;
-    const int k      = SUMMARY ? q - J : q;  // real column index
+    const bool basis = BASIS && q < J;
+    const int k      = BASIS ? q - J : q;  // real column index
     // real columns of this group: [kc0, kc0 + kw)
-    const int kc0 = SUMMARY ? (q0 > J ? q0 - J : 0) : q0;
-    const int kc1 = SUMMARY ? (q0 + NT - J < a.K ? q0 + NT - J : a.K) : (q0 + NT < a.K ? q0 + NT : a.K);
+    const int kc0 = BASIS ? (q0 > J ? q0 - J : 0) : q0;
+    const int kc1 = BASIS ? (q0 + NT - J < a.K ? q0 + NT - J : a.K) : (q0 + NT < a.K ? q0 + NT : a.K);
     const int kw  = kc1 > kc0 ? kc1 - kc0 : 0;
     double Fk[J];
+    double mk[(SUMMARY && !SOLVE) ? J : 1];  // products: the chunk's propagator product (thread of column 0)
+#pragma unroll
+    for (int j = 0; j < ((SUMMARY && !SOLVE) ? J : 1); ++j) mk[j] = 1.0;
 #pragma unroll
     for (int j = 0; j < J; ++j) Fk[j] = (basis && j == q) ? 1.0 : 0.0;
     if (!SUMMARY && a.carry && have) {
@@ -759,18 +766,37 @@ __global__ void __launch_bounds__(kColThreads, 2) csweep_tile_kernel(SweepArgs a
               sm    = fma(av[j], Fk[j], sm);
             }
             const double y = basis ? 0.0 : tb[oY + s * yw + (k - kc0)];
-            const double z = y - sm;
-            if (!SUMMARY) Z[n * (int64_t)a.K + k] = zdiv ? z * dinv[r] : z;
+            double rr;
+            if (SOLVE) {
+              rr = y - sm;
+              if (!SUMMARY) Z[n * (int64_t)a.K + k] = zdiv ? rr * dinv[r] : rr;
+            } else {
+              rr = y;
+              if (!SUMMARY) Z[n * (int64_t)a.K + k] += sm;
+              if (SUMMARY && q == 0) {
+#pragma unroll
+                for (int j = 0; j < J; ++j) mk[j] *= p[j];
+              }
+            }
             lds_row<J>(tb + oB + s * J, bv);
 #pragma unroll
-            for (int j = 0; j < J; ++j) Fk[j] = fma(bv[j], z, Fk[j]);
+            for (int j = 0; j < J; ++j) Fk[j] = fma(bv[j], rr, Fk[j]);
           }
         }
       }
       __syncthreads();
       issue(kt + 2);
     }
-    if (SUMMARY && have) {
+    if (SUMMARY && !SOLVE && have) {
+      double *e = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J + J * a.K);
+      if (q == 0) {
+#pragma unroll
+        for (int j = 0; j < J; ++j) e[j] = mk[j];
+      }
+#pragma unroll
+      for (int j = 0; j < J; ++j) e[J + j + J * k] = Fk[j];
+    }
+    if (SUMMARY && SOLVE && have) {
       double *e = a.leaves + (b * a.node_stride + leaf) * (int64_t)(J * J + J * a.K);
       if (basis) {
 #pragma unroll

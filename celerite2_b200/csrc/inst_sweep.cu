@@ -112,10 +112,10 @@ static int launch_sweep_rev_group(SweepRevArgs &a, const ScanBuffers &sb, double
   return C2B_OK;
 }
 
-// K > 1 solves with a compile-time width: one CTA per chunk, one thread per column (csweep_tile_kernel)
+// K > 1 sweeps (solves and products) with a compile-time width: one CTA per chunk, one thread per column (csweep_tile_kernel)
 template <int JT, bool SOLVE, bool LOWER>
 static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
-  if constexpr (JT > 0 && SOLVE) {
+  if constexpr (JT > 0) {
     auto threads_for = [](int ncol) {
       int nt = (ncol + 31) / 32 * 32;
       return nt > kColThreads ? kColThreads : nt;
@@ -124,16 +124,20 @@ static int launch_sweep_columns(SweepArgs &a, const ScanBuffers &sb, cudaStream_
     if (a.C > 1) {
       a.leaves      = sb.nodes;
       a.node_stride = sb.node_stride;
-      const int nt  = threads_for(JT + a.K);
+      const int nt  = threads_for(SOLVE ? JT + a.K : a.K);
       const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
-      C2B_LAUNCH("csweep_summary_kernel", stream, (launch_k(csweep_tile_kernel<JT, LOWER, true>, grid, nt, smem, stream, a)));
-      int rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      C2B_LAUNCH("csweep_summary_kernel", stream, (launch_k(csweep_tile_kernel<JT, LOWER, true, SOLVE>, grid, nt, smem, stream, a)));
+      int rc;
+      if (SOLVE)
+        rc = run_scan<AffV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
+      else
+        rc = run_scan<DiagV<JT>>(a.J, a.K, a.batch, a.C, sb.nodes, sb.states, nullptr, stream);
       if (rc) return rc;
       a.carry = sb.states;
     }
     const int nt      = threads_for(a.K);
     const size_t smem = csweep_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
-    C2B_LAUNCH("csweep_apply_kernel", stream, (launch_k(csweep_tile_kernel<JT, LOWER, false>, grid, nt, smem, stream, a)));
+    C2B_LAUNCH("csweep_apply_kernel", stream, (launch_k(csweep_tile_kernel<JT, LOWER, false, SOLVE>, grid, nt, smem, stream, a)));
   }
   return C2B_OK;
 }
@@ -146,7 +150,7 @@ int launch_sweep(SweepArgs &a, const ScanBuffers &sb, cudaStream_t stream) {
   }
   if (JT > 0 && JT <= 16 && a.K == 1 && (a.seg.phase != 0 || !no_group_kernels()))
     return launch_sweep_group<JT, SOLVE, LOWER>(a, sb, stream);
-  if (JT > 0 && SOLVE && a.K > 1 && !no_group_kernels()) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
+  if (JT > 0 && a.K > 1 && !no_group_kernels()) return launch_sweep_columns<JT, SOLVE, LOWER>(a, sb, stream);
   unsigned grid, block;
   size_t smem;
   int rcs;
