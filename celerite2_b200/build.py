@@ -33,7 +33,7 @@ FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxe
 _COMMON = ["common.cuh", "monoids.cuh", "coop.cuh", "scan.cuh", "fold.cuh", "args.cuh", "host_common.cuh"]
 _EXTRA = {
     "api_misc.cu": ["misc.cuh"],
-    "inst_sweep.cu": ["sweep.cuh", "group.cuh", "gsweep.cuh"],
+    "inst_sweep.cu": ["sweep.cuh", "group.cuh", "gsweep.cuh", "csweep_rev.cuh"],
     "inst_factor.cu": ["factor.cuh", "group.cuh", "gfactor.cuh", "gfactor_rev.cuh"],
 }
 

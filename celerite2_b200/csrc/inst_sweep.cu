@@ -4,6 +4,7 @@
 
 #include "sweep.cuh"
 #include "gsweep.cuh"
+#include "csweep_rev.cuh"
 
 #ifndef C2B_JT
 #error "compile with -DC2B_JT=<width> (0 = run-time width)"
@@ -216,10 +217,28 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
     if (rc) return rc;
     a.carry = sb.states;
   }
-  rcs = staged_shape(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
-                     &smem);
-  if (rcs) return rcs;
-  C2B_LAUNCH("sweep_rev_apply_kernel", stream, launch_k(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, grid, block, smem, stream, a));
+  bool tiled = false;
+  if constexpr (JT > 0) {
+    // K > 1, compiled width: CTA per chunk, thread per column, panel sums for the cotangents shared by the columns
+    if (a.K > 1 && !no_group_kernels()) {
+      int nt = (a.K + 31) / 32 * 32;
+      if (nt > kColThreads) nt = kColThreads;
+      const size_t sm = csweep_rev_smem_doubles<JT>(nt < a.K ? nt : a.K, nt) * sizeof(double);
+      if (sm <= 200 * 1024) {
+        if (sm > 48 * 1024)
+          C2B_CUDA(cudaFuncSetAttribute(csweep_rev_tile_kernel<JT, SOLVE, LOWER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        C2B_LAUNCH("csweep_rev_apply_kernel", stream,
+                   (launch_k(csweep_rev_tile_kernel<JT, SOLVE, LOWER>, (unsigned)(a.batch * a.C), nt, sm, stream, a)));
+        tiled = true;
+      }
+    }
+  }
+  if (!tiled) {
+    rcs = staged_shape(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
+                       &smem);
+    if (rcs) return rcs;
+    C2B_LAUNCH("sweep_rev_apply_kernel", stream, launch_k(sweep_rev_apply_kernel<JT, SOLVE, LOWER>, grid, block, smem, stream, a));
+  }
   C2B_LAUNCH("rev_finalize_kernel", stream, launch_k(rev_finalize_kernel, dim3((unsigned)((a.C + 1023) / 1024), (unsigned)a.batch), 1024, 0, stream, a.N, a.C, a.L, a.J, LOWER, a.bc_part, a.bt_edge, a.bt, bc, false));
   return C2B_OK;
 }

@@ -25,4 +25,9 @@ def timeit(fn, steps=10, warm=3):
 out = dict(mode="generic" if os.environ.get("C2B_NO_GROUP") else "tile kernels",
            matmul_lower=timeit(lambda: ops.matmul_lower(t, c, U, V, Y)), matmul_upper=timeit(lambda: ops.matmul_upper(t, c, U, V, Y)),
            dot_tril=timeit(lambda: ops.dot_tril(t, c, U, W, d, Y)), solve_lower=timeit(lambda: ops.solve_lower(t, c, U, W, Y)))
+Z, F = ops.solve_lower(t, c, U, W, Y, workspace=True)
+bZ = torch.randn_like(Z)
+out["solve_lower_rev"] = timeit(lambda: ops.solve_lower_rev(t, c, U, W, Y, Z, F, bZ), steps=3, warm=1)
+Zm, Fm = ops.matmul_lower(t, c, U, V, Y, workspace=True)
+out["matmul_lower_rev"] = timeit(lambda: ops.matmul_lower_rev(t, c, U, V, Y, Zm, Fm, bZ), steps=3, warm=1)
 print(json.dumps(out))
