@@ -208,4 +208,136 @@ __global__ void __launch_bounds__(kColThreads, 1) csweep_rev_tile_kernel(SweepRe
   if (tid == 0) a.bt_edge[b * a.C + chunk] = edge;
 }
 
+// ---- summary pass: the chunk's map of the adjoint state, column by column ----------------------------------------------
+// solves: bF -> P (I -/+ a b^T) bF -/+ P a bz0 per row: J unit-vector columns give the J x J head, the K real columns (from
+// zero, fed by bZ) the offsets: the AffV element of the forward pass with the roles of the row vectors exchanged.
+// products: bF -> p o (bF + a bz0): diagonal-affine; the head is the chunk's product of propagators, exp(c * (time spanned)).
+// dynamic shared memory (doubles): 2 x [A R*J | B R*J | t R+2 (+pad) | bZ R*yw], P R*J, c J
+template <int J>
+__host__ __device__ inline size_t csweep_rev_summary_smem_doubles(int yw) {
+  constexpr int R = kTileRows;
+  const int tb    = 2 * R * J + ((R + 2 + 1) & ~1) + R * yw;
+  return (size_t)2 * tb + R * J + J;
+}
+
+template <int J, bool SOLVE, bool LOWER>
+__global__ void __launch_bounds__(kColThreads, 2) csweep_rev_summary_kernel(SweepRevArgs a) {
+  pdl_prologue();
+  constexpr int R   = kTileRows;
+  constexpr bool UP = !LOWER;
+  constexpr int dir = UP ? 1 : -1;
+  constexpr int oB = R * J, oT = 2 * R * J, oZ = oT + ((R + 2 + 1) & ~1);
+  extern __shared__ __align__(16) double cr_smem[];
+  const int NT        = blockDim.x;
+  const int tid       = threadIdx.x;
+  const int64_t chunk = blockIdx.x % a.C, b = blockIdx.x / a.C;
+  const int64_t n0    = chunk * a.L;
+  const int64_t n1    = n0 + a.L < a.N ? n0 + a.L : a.N;
+  const int K         = a.K;
+  const int ncol      = SOLVE ? J + K : K;
+  const int yw        = NT < K ? NT : K;
+  const int TB        = oZ + R * yw;
+  double *pb  = cr_smem + 2 * TB;
+  double *csm = pb + R * J;
+  const double *t = a.t + b * a.t_bs;
+  const int64_t NJ = a.N * J, NK = a.N * (int64_t)K;
+  const double *A = a.A + b * NJ, *B = a.B + b * NJ, *bZ = a.bZ + b * NK;
+  const int64_t leaf = LOWER ? a.C - 1 - chunk : chunk;
+  const int es       = SOLVE ? J * J + J * K : J + J * K;
+  double *e          = a.leaves + (b * a.node_stride + leaf) * (int64_t)es;
+  const CtaCopy cp{tid, NT};
+  const bool wide = (J % 2 == 0) && (((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) == 0);
+  if (tid < J) csm[tid] = (a.c + b * a.c_bs)[tid];
+  const int cnt       = (int)(n1 - n0);
+  const int ntile     = (cnt + R - 1) / R;
+  const int64_t nf    = UP ? n0 : n1 - 1;
+  const int64_t nlast = LOWER ? a.tmin : a.tmax;
+  for (int q0 = 0; q0 < ncol; q0 += NT) {
+    const int q      = q0 + tid;
+    const bool have  = q < ncol;
+    const bool basis = SOLVE && q < J;
+    const int k      = SOLVE ? q - J : q;
+    const int kc0 = SOLVE ? (q0 > J ? q0 - J : 0) : q0;
+    const int kc1 = SOLVE ? (q0 + NT - J < K ? q0 + NT - J : K) : (q0 + NT < K ? q0 + NT : K);
+    const int kw  = kc1 > kc0 ? kc1 - kc0 : 0;
+    double G[J];
+#pragma unroll
+    for (int j = 0; j < J; ++j) G[j] = (basis && j == q) ? 1.0 : 0.0;
+    auto issue = [&](int kt) {
+      if (kt < ntile) {
+        const int rows   = cnt - kt * R < R ? cnt - kt * R : R;
+        const int64_t lo = UP ? n0 + (int64_t)kt * R : n1 - (int64_t)kt * R - rows;
+        const int pad    = UP ? 0 : R - rows;
+        double *tb       = cr_smem + (kt & 1) * TB;
+        cp.run(tb + pad * J, A + lo * J, rows * J, wide);
+        if (SOLVE) cp.run(tb + oB + pad * J, B + lo * J, rows * J, wide);
+        cp.run_t(tb + oT + pad, t, lo - 1, rows + 2, a.tmin, a.tmax);
+        for (int r = 0; r < rows; ++r) cp.run(tb + oZ + (pad + r) * yw, bZ + (lo + r) * (int64_t)K + kc0, kw, false);
+      }
+      cp_async_commit();
+    };
+    __syncthreads();
+    issue(0);
+    issue(1);
+    for (int kt = 0; kt < ntile; ++kt) {
+      cp_async_wait<1>();
+      __syncthreads();
+      const double *tb = cr_smem + (kt & 1) * TB;
+      const int rows   = cnt - kt * R < R ? cnt - kt * R : R;
+      for (int i = tid; i < R * J; i += NT) {
+        const int r = i / J, j = i - r * J;
+        const int s = UP ? r : R - 1 - r;
+        const double dt = LOWER ? tb[oT + s] - tb[oT + s + 1] : tb[oT + s + 1] - tb[oT + s + 2];
+        pb[i] = exp(csm[j] * dt);
+      }
+      __syncthreads();
+      const int64_t nt = nf + (int64_t)dir * kt * R;
+      if (have) {
+#pragma unroll 2
+        for (int r = 0; r < R; ++r) {
+          if (r < rows && nt + dir * r != nlast) {
+            const int s = UP ? r : R - 1 - r;
+            double p[J], av[J];
+            lds_row<J>(pb + r * J, p);
+            lds_row<J>(tb + s * J, av);
+            double bz = basis ? 0.0 : tb[oZ + s * yw + (k - kc0)];
+            if (SOLVE) {
+              double bv[J];
+              lds_row<J>(tb + oB + s * J, bv);
+#pragma unroll
+              for (int j = 0; j < J; ++j) bz = fma(bv[j], G[j], bz);
+#pragma unroll
+              for (int j = 0; j < J; ++j) G[j] = p[j] * fma(-av[j], bz, G[j]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < J; ++j) G[j] = p[j] * fma(av[j], bz, G[j]);
+            }
+          }
+        }
+      }
+      __syncthreads();
+      issue(kt + 2);
+    }
+    if (have) {
+      if (basis) {
+#pragma unroll
+        for (int j = 0; j < J; ++j) e[j * J + q] = G[j];
+      } else {
+        double *bb = e + (SOLVE ? J * J : J);
+#pragma unroll
+        for (int j = 0; j < J; ++j) bb[j + J * k] = G[j];
+      }
+    }
+  }
+  if (!SOLVE && tid < J) {
+    // product of the propagators the chunk applies (rows with a predecessor only): exp(c * time spanned)
+    double dt;
+    if (LOWER)
+      dt = t[n0 > 0 ? n0 - 1 : 0] - t[n1 - 1];
+    else
+      dt = t[n0] - t[n1 < a.N ? n1 : a.N - 1];
+    e[tid] = exp(csm[tid] * dt);
+  }
+}
+
 }  // namespace c2b

@@ -198,7 +198,21 @@ int launch_sweep_rev(SweepRevArgs &a, const ScanBuffers &sb, double *bc, cudaStr
     a.leaves      = sb.nodes;
     a.node_stride = sb.node_stride;
     const int ncol = SOLVE ? a.J + a.K : a.K;
-    if (SOLVE && a.K == 1) {
+    bool tiled_summary = false;
+    if constexpr (JT > 0) {
+      if (a.K > 1 && !no_group_kernels()) {
+        int nt = (ncol + 31) / 32 * 32;
+        if (nt > kColThreads) nt = kColThreads;
+        const size_t sm = csweep_rev_summary_smem_doubles<JT>(nt < a.K ? nt : a.K) * sizeof(double);
+        if (sm <= 48 * 1024) {
+          C2B_LAUNCH("csweep_rev_summary_kernel", stream,
+                     (launch_k(csweep_rev_summary_kernel<JT, SOLVE, LOWER>, (unsigned)(a.batch * a.C), nt, sm, stream, a)));
+          tiled_summary = true;
+        }
+      }
+    }
+    if (tiled_summary) {
+    } else if (SOLVE && a.K == 1) {
       rcs = staged_shape(sweep_rev_summary1_kernel<JT, LOWER>, a.batch * a.C, JT > 0, kSweepRevSlots, SweepRevRow<JT>::ROWD, &grid, &block,
                          &smem);
       if (rcs) return rcs;
