@@ -114,6 +114,31 @@ def test_apply_inverse_and_dot_tril(env, name, N, K, chunks):
         assert relerr(Kd @ want_inv, Y) < 1e-9
 
 
+# ---- more right-hand sides than the tile kernels have threads (256): the column-group loops and their accumulation ------
+@pytest.mark.parametrize("chunks", [0, 5])
+def test_more_columns_than_threads(env, chunks):
+    ops, T, H, torch = env
+    N, K = 300, 300
+    P, t, c, a, U, V, d, W = _factorised("sum4", N, 43)
+    rng = np.random.default_rng(44)
+    Y = rng.standard_normal((N, K))
+    bZ = rng.standard_normal((N, K))
+    tt, cc, UU, YY = map(T, (t, c, U, Y))
+    ops.set_chunks_per_series(chunks)
+    try:
+        for op, Bm in (("solve_lower", W), ("solve_upper", W), ("matmul_lower", V), ("matmul_upper", V)):
+            Z_o, F_o = P.sweep(op, t, c, U, Bm, Y)
+            Z, F = getattr(ops, op)(tt, cc, UU, T(Bm), YY, workspace=True)
+            assert relerr(H(Z), Z_o) < TOL, op
+            assert relerr(H(F), F_o) < TOL, op + " workspace"
+            want = P.sweep_rev(op, t, c, U, Bm, Y, Z_o, F_o, bZ)
+            got = getattr(ops, op + "_rev")(tt, cc, UU, T(Bm), YY, T(Z_o), T(F_o), T(bZ))
+            for nm, g, w in zip(("bt", "bc", "bU", "bB", "bY"), got, want):
+                assert relerr(H(g), w) < TOL, "%s_rev %s" % (op, nm)
+    finally:
+        ops.set_chunks_per_series(0)
+
+
 # ---- the bench workload at full size against the reference's own core -----------------------------------------------
 def _c2_reference(N):
     import oracle
