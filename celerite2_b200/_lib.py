@@ -30,6 +30,7 @@ _SIGS = {
     "c2b_general_matmul_lower": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_general_matmul_upper": [_i64, _i64, _i32, _i32] + [_vp] * 8 + [_vp, _sz, _vp],
     "c2b_norm_logdet": [_i64, _i64] + [_vp] * 5 + [_vp, _sz, _vp],
+    "c2b_norm_logdet_loglike": [_i64, _i64] + [_vp] * 6 + [_vp, _sz, _vp],
     "c2b_add_inplace": [_i64, _vp, _vp, _vp],
     "c2b_term_coefficients": [_i32, _i64, _vp, ctypes.c_double, _i32, _i32, _i32, _i32, _i32] + [_vp] * 6 + [_vp, _vp],
     "c2b_term_coefficients_rev": [_i32, _i64, _vp, ctypes.c_double, _i32, _i32, _i32, _i32, _i32] + [_vp] * 6 + [_vp, _vp],

@@ -455,9 +455,8 @@ int c2b_get_celerite_matrices_rev(int32_t layout, int64_t N, int32_t Jr, int32_t
   return C2B_OK;
 }
 
-int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd, void *scratch,
-                    size_t scratch_bytes, void *stream_) {
-  c2b::OpScope _op("c2b_norm_logdet");
+static int norm_logdet_impl(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *loglike, double *bz,
+                            double *bd, void *scratch, size_t scratch_bytes, void *stream_) {
   using namespace c2b;
   int rc = check_common(N, 1, batch);
   if (rc) return rc;
@@ -469,8 +468,21 @@ int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, 
   const int ctas = red_ctas(N);
   dim3 grid((unsigned)ctas, (unsigned)batch);
   C2B_LAUNCH("norm_logdet_kernel", stream, launch_k(norm_logdet_kernel, grid, kRedThreads, 0, stream, N, d, z, bz, bd, (double *)sc.ptr, ctas));
-  C2B_LAUNCH("norm_logdet_final_kernel", stream, launch_k(norm_logdet_final_kernel, (unsigned)batch, 64, 0, stream, (const double *)sc.ptr, ctas, out));
+  C2B_LAUNCH("norm_logdet_final_kernel", stream,
+             launch_k(norm_logdet_final_kernel, (unsigned)batch, 64, 0, stream, (const double *)sc.ptr, ctas, out, loglike,
+                      0.5 * (double)N * 1.8378770664093453 /* log(2 pi) */));
   return C2B_OK;
+}
+int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd, void *scratch,
+                    size_t scratch_bytes, void *stream_) {
+  c2b::OpScope _op("c2b_norm_logdet");
+  return norm_logdet_impl(N, batch, d, z, out, nullptr, bz, bd, scratch, scratch_bytes, stream_);
+}
+int c2b_norm_logdet_loglike(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *loglike, double *bz,
+                            double *bd, void *scratch, size_t scratch_bytes, void *stream_) {
+  c2b::OpScope _op("c2b_norm_logdet");
+  C2B_REQUIRE(loglike, "null data pointer");
+  return norm_logdet_impl(N, batch, d, z, out, loglike, bz, bd, scratch, scratch_bytes, stream_);
 }
 
 int c2b_add_inplace(int64_t n, const double *x, double *y, void *stream_) {

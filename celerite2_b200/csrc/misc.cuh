@@ -186,9 +186,11 @@ __global__ void norm_logdet_kernel(int64_t N, const double *d, const double *z, 
     part[(b * ctas + blockIdx.x) * 2 + 1] = s2[0];
   }
 }
-__global__ void norm_logdet_final_kernel(const double *part, int ctas, double *out) {
+// ll (nullable): loglike[b] = -0.5 (chi2 + logdet) - half_n_log_2pi, written by the same launch (python/celerite2/core.py:407-428)
+__global__ void norm_logdet_final_kernel(const double *part, int ctas, double *out, double *ll, double half_n_log_2pi) {
   pdl_prologue();
   // warp 0: log-det, warp 1: chi^2
+  __shared__ double both[2];
   const int64_t b = blockIdx.x;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   if (wid < 2) {
@@ -196,8 +198,13 @@ __global__ void norm_logdet_final_kernel(const double *part, int ctas, double *o
     for (int k = lane; k < ctas; k += 32) s += part[(b * ctas + k) * 2 + wid];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (lane == 0) out[b * 2 + wid] = s;
+    if (lane == 0) {
+      out[b * 2 + wid] = s;
+      both[wid]        = s;
+    }
   }
+  __syncthreads();
+  if (ll && threadIdx.x == 0) ll[b] = -0.5 * (both[0] + both[1]) - half_n_log_2pi;
 }
 
 __global__ void add_inplace_kernel(int64_t n, const double *x, double *y) {

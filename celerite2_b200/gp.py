@@ -36,8 +36,8 @@ def _front_value(coeffs, t, diag, layout):
 def _back_value(y, diag, front):
     t, c, U, W, d, status = front
     Z, _ = ops.solve_lower(t, c, U, W, y.unsqueeze(-1))
-    out, _, _ = ops.norm_logdet(d, Z.squeeze(-1))
-    ll = -0.5 * (out[..., 0] + out[..., 1] + diag.shape[-1] * math.log(2 * math.pi))
+    ll = torch.empty(diag.shape[:-1], dtype=torch.float64, device=diag.device)
+    ops.norm_logdet(d, Z.squeeze(-1), loglike=ll.reshape(-1))  # (the value comes out of the reduction's own launch)
     return dict(loglike=ll, status=status)
 
 
@@ -48,16 +48,37 @@ def _front(coeffs, t, diag, layout):
     return c, a, U, V, d, W, S, status
 
 
-def _back(coeffs, t, y, diag, front, layout, want_data_grads):
+def _packed_views(coeffs, diag):
+    """one result buffer [loglike | d/d ar | d/d cr | d/d ac | d/d bc | d/d cc | d/d dc] (series-major blocks for a batch) and
+    views of its seven parts shaped like the quantities they hold"""
+    lead = tuple(diag.shape[:-1])
+    nb = int(torch.Size(lead).numel()) if lead else 1
+    sizes = [nb] + [v.numel() for v in coeffs]
+    packed = torch.empty(sum(sizes), dtype=torch.float64, device=diag.device)
+    offs = [0]
+    for n in sizes:
+        offs.append(offs[-1] + n)
+    views = [packed[offs[0]:offs[1]].view(lead)] + [packed[offs[i + 1]:offs[i + 2]].view(v.shape) for i, v in enumerate(coeffs)]
+    return packed, views
+
+
+def _back(coeffs, t, y, diag, front, layout, want_data_grads, packed_views=None):
+    """packed_views (from _packed_views): the log-likelihood and the coefficient gradients are written straight into them by
+    the reduction and assembly-adjoint kernels (no host-side arithmetic, no concatenation)."""
     c, a, U, V, d, W, S, status = front
     Y = y.unsqueeze(-1)
     Z, F = ops.solve_lower(t, c, U, W, Y, workspace=True)
-    out, bz, bd = ops.norm_logdet(d, Z.squeeze(-1), want_grad=True)
     N = diag.shape[-1]
-    ll = -0.5 * (out[..., 0] + out[..., 1] + N * math.log(2 * math.pi))
+    if packed_views is not None:
+        ll = packed_views[0]
+        out, bz, bd = ops.norm_logdet(d, Z.squeeze(-1), want_grad=True, loglike=ll.reshape(-1))
+    else:
+        out, bz, bd = ops.norm_logdet(d, Z.squeeze(-1), want_grad=True)
+        ll = -0.5 * (out[..., 0] + out[..., 1] + N * math.log(2 * math.pi))
     bt, bc, bU, bW, bY = ops.solve_lower_rev(t, c, U, W, Y, Z, F, bz.unsqueeze(-1))
     _, _, ba, _, bV = ops.factor_rev(t, c, a, U, V, d, W, S, bd, bW, accumulate_into=(bt, bc, bU))
-    g = ops.get_celerite_matrices_rev(*coeffs, t, bc, ba, bU, bV, b_x=bt, layout=layout, want_diag=want_data_grads)
+    g = ops.get_celerite_matrices_rev(*coeffs, t, bc, ba, bU, bV, b_x=bt, layout=layout, want_diag=want_data_grads,
+                                      out=packed_views[1:] if packed_views is not None else None)
     res = dict(loglike=ll, status=status, grads=dict(zip(COEFF_NAMES, g[:6])))
     # the operator-level outputs (views, nothing copied): what the parity checks compare with the reference's arrays
     res["raw"] = dict(c=c, a=a, U=U, V=V, d=d, W=W, S=S, Z=Z, F=F, bt=bt, bc=bc, ba=ba, bU=bU, bV=bV, bY=bY)
@@ -104,10 +125,10 @@ class GraphedLogLikelihood:
                 self._front = _front(self.coeffs, t, diag, layout) if grad else _front_value(self.coeffs, t, diag, layout)
             with torch.cuda.graph(self.g_back, pool=self.g_front.pool()):
                 if grad:
-                    self.result = _back(self.coeffs, t, y, diag, self._front, layout, False)
                     # [loglike | d/d ar | d/d cr | d/d ac | d/d bc | d/d cc | d/d dc] in one tensor (series-major blocks
-                    # for a batch: all log-likelihoods, then all d/d ar, ...), packed inside the graph
-                    self.packed = torch.cat([self.result["loglike"].reshape(-1)] + [self.result["grads"][nm].reshape(-1) for nm in COEFF_NAMES])
+                    # for a batch: all log-likelihoods, then all d/d ar, ...), written in place by the kernels
+                    self.packed, views = _packed_views(self.coeffs, diag)
+                    self.result = _back(self.coeffs, t, y, diag, self._front, layout, False, packed_views=views)
                 else:
                     self.result = _back_value(y, diag, self._front)
                     self.packed = self.result["loglike"].reshape(-1)

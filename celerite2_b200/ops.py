@@ -132,8 +132,9 @@ def get_celerite_matrices(ar, cr, ac, bc, cc, dc, x, diag, layout="blocked", out
     return c, a, U, V
 
 
-def get_celerite_matrices_rev(ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V, b_x=None, layout="blocked", want_diag=True):
-    """Adjoint of the assembly -> (b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_diag).  b_x (if given) is accumulated into."""
+def get_celerite_matrices_rev(ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V, b_x=None, layout="blocked", want_diag=True, out=None):
+    """Adjoint of the assembly -> (b_ar, b_cr, b_ac, b_bc, b_cc, b_dc, b_x, b_diag).  b_x (if given) is accumulated into.
+    out: optional six contiguous tensors that receive the coefficient cotangents (e.g. views of one packed result buffer)."""
     ar, cr, ac, bc, cc, dc, x, b_a, b_U, b_V = [_f64(v, "arg") for v in (ar, cr, ac, bc, cc, dc, x, b_a, b_U, b_V)]
     batch = b_a.shape[0] if b_a.dim() == 2 else 1
     N = b_a.shape[-1]
@@ -142,7 +143,13 @@ def get_celerite_matrices_rev(ar, cr, ac, bc, cc, dc, x, b_c, b_a, b_U, b_V, b_x
     lead = (batch,) if b_a.dim() == 2 else ()
     dev = b_a.device
     new = lambda n: torch.empty(lead + (n,), dtype=torch.float64, device=dev)
-    b_ar, b_cr, b_ac, b_bc, b_cc, b_dc = new(Jr), new(Jr), new(Jc), new(Jc), new(Jc), new(Jc)
+    if out is not None:
+        b_ar, b_cr, b_ac, b_bc, b_cc, b_dc = out
+        for v, n in zip(out, (Jr, Jr, Jc, Jc, Jc, Jc)):
+            if v.numel() != batch * n or not v.is_contiguous() or v.dtype != torch.float64:
+                raise ValueError("out: six contiguous float64 tensors shaped like the coefficient arrays")
+    else:
+        b_ar, b_cr, b_ac, b_bc, b_cc, b_dc = new(Jr), new(Jr), new(Jc), new(Jc), new(Jc), new(Jc)
     if b_x is None:
         b_x = torch.zeros(lead + (N,), dtype=torch.float64, device=dev)
     b_diag = new(N) if want_diag else None
@@ -322,9 +329,10 @@ def general_matmul_upper(t1, t2, c, U, V, Y, Z=None, F=None):
 
 
 # ---- reductions ----------------------------------------------------------------------------------------------
-def norm_logdet(d, z, want_grad=False):
+def norm_logdet(d, z, want_grad=False, loglike=None):
     """-> (out, bz, bd): out[..., 0] = sum log d, out[..., 1] = sum z^2/d; bz, bd seed the backward pass of
-    loglike = -0.5 (chi2 + logdet + N log 2 pi) when want_grad."""
+    loglike = -0.5 (chi2 + logdet + N log 2 pi) when want_grad.  loglike: optional tensor of `batch` doubles that receives
+    that value from the same launch (no follow-up arithmetic on the host side)."""
     d, z = _f64(d, "d"), _f64(z, "z")
     batch = d.shape[0] if d.dim() == 2 else 1
     N = d.shape[-1]
@@ -333,7 +341,13 @@ def norm_logdet(d, z, want_grad=False):
     bz = torch.empty_like(z) if want_grad else None
     bd = torch.empty_like(d) if want_grad else None
     buf = _scratch_buffer("red", max(256 * 1024, batch * 592 * 16 + 256), dev)
-    check(lib.c2b_norm_logdet(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(bz), _ptr(bd), buf.data_ptr(), buf.numel(), _stream()))
+    if loglike is not None:
+        if loglike.numel() != batch or not loglike.is_contiguous():
+            raise ValueError("loglike must be a contiguous tensor of batch doubles")
+        check(lib.c2b_norm_logdet_loglike(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(_f64(loglike, "loglike")), _ptr(bz), _ptr(bd),
+                                          buf.data_ptr(), buf.numel(), _stream()))
+    else:
+        check(lib.c2b_norm_logdet(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(bz), _ptr(bd), buf.data_ptr(), buf.numel(), _stream()))
     return out, bz, bd
 
 

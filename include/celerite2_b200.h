@@ -325,6 +325,10 @@ int c2b_general_matmul_upper(int64_t N, int64_t M, int32_t J, int32_t K, const d
  */
 int c2b_norm_logdet(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *bz, double *bd,
                     void *scratch, size_t scratch_bytes, void *stream);
+/* The same, and loglike (batch) = -0.5 (chi2 + logdet + N log 2 pi) from the same launch: what
+ * GaussianProcess.log_likelihood returns for a zero-mean process (python/celerite2/core.py:407-428). */
+int c2b_norm_logdet_loglike(int64_t N, int64_t batch, const double *d, const double *z, double *out, double *loglike, double *bz,
+                            double *bd, void *scratch, size_t scratch_bytes, void *stream);
 
 /*
  * solve_lower for callers that cannot allocate device memory.  (No counterpart in the reference.)
