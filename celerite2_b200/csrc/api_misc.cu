@@ -167,7 +167,10 @@ Plan make_plan(int64_t N, int64_t batch, int64_t cols, int J, int ctas_per_sm, i
     // 0.499 ms with 32-row chunks (16 rows: no faster, and grad_dc leaves the 1e-10 band); from 500k on the one-wave
     // target decides and the floor is not reached
     const int64_t pts      = N * batch;
-    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : (pts <= 16384 ? 16 : (pts <= 400000 ? 32 : 64));
+    // (r03g / r03h: c1, N = 1000: 69.9 us with 16-row chunks, 53.5 us with 8-row chunks, no further gain below; at
+    // N = 4000 - 5000 the extra scan levels of 8-row chunks push W of the ill-conditioned J = 6 kernel to 1.4e-10, so the
+    // 8-row floor is for the really short series only)
+    const int64_t min_rows = env_min_rows > 0 ? env_min_rows : (pts <= 2048 ? 8 : (pts <= 16384 ? 16 : (pts <= 400000 ? 32 : 64)));
     const int64_t maxC     = N / min_rows;
     if (C > maxC) C = maxC;
   }
