@@ -342,8 +342,8 @@ def norm_logdet(d, z, want_grad=False, loglike=None):
     bd = torch.empty_like(d) if want_grad else None
     buf = _scratch_buffer("red", max(256 * 1024, batch * 592 * 16 + 256), dev)
     if loglike is not None:
-        if loglike.numel() != batch or not loglike.is_contiguous():
-            raise ValueError("loglike must be a contiguous tensor of batch doubles")
+        if loglike.numel() != batch or not loglike.is_contiguous() or loglike.dtype != torch.float64 or loglike.device != dev:
+            raise ValueError("loglike must be a contiguous float64 tensor of batch elements on the device of d")
         check(lib.c2b_norm_logdet_loglike(N, batch, _ptr(d), _ptr(z), _ptr(out), _ptr(_f64(loglike, "loglike")), _ptr(bz), _ptr(bd),
                                           buf.data_ptr(), buf.numel(), _stream()))
     else:
